@@ -1,0 +1,272 @@
+/*
+ * spk_cuda.h — C ABI of the B200-native `cuda` path-tracing pipeline for Sparkle.
+ *
+ * This is the drop-in boundary. The reference has no FFI: its renderers are C++
+ * classes behind `Renderer::CreateRenderer` (libraries/source/renderer/renderer/Renderer.cpp:17-53).
+ * A `CudaRenderer : Renderer` (see sparkle_b200/host/renderer.h and INTEGRATION.md) binds exactly the
+ * entry points below. Plain pointers and sizes only; no C++ / torch types cross this line.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error (SpkStatus); spk_cuda_last_error() gives text.
+ *     Mirrors the reference's "bool/nullptr + Log(Error)" convention (AppFramework.cpp:200-205); nothing
+ *     throws across the boundary.
+ *   - the context owns all device memory; the caller owns all host memory. Host pointers in
+ *     SpkSceneDesc are borrowed for the duration of the call only.
+ *   - one context == one CUDA device == one stream. Multi-GPU = one process (context) per GPU, spp
+ *     interleaved by (first_sample, sample_stride), accumulators summed by the caller with one NCCL
+ *     reduce on the pointer spk_cuda_accum_device_ptr() returns.
+ *   - there is NO CPU fallback: without a CUDA device spk_cuda_create fails with SPK_ERR_NO_DEVICE.
+ */
+#ifndef SPK_CUDA_H_
+#define SPK_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPK_ABI_VERSION 1u
+#define SPK_INVALID_ID 0xFFFFFFFFu
+
+typedef enum SpkStatus {
+    SPK_OK = 0,
+    SPK_ERR_INVALID_ARGUMENT = -1,
+    SPK_ERR_NO_DEVICE = -2,
+    SPK_ERR_CUDA = -3,
+    SPK_ERR_OUT_OF_MEMORY = -4,
+    SPK_ERR_NO_SCENE = -5,
+    SPK_ERR_UNSUPPORTED = -6
+} SpkStatus;
+
+/* ---- acceleration structures ------------------------------------------------------------------
+ * Node layout is that of bvh::v2::Node<float,3> (madmann91/bvh @5a9d759c, the library behind
+ * core/math/BVH.h:18-19): bounds = {min.x,max.x,min.y,max.y,min.z,max.z}, index = first_id<<4 |
+ * prim_count; prim_count==0 marks an inner node whose children are nodes[first_id], nodes[first_id+1];
+ * node 0 is the root. `node_stride` is 28 (the raw library struct) or 32 (padded). `prim_ids` maps
+ * leaf slots to primitive indices (bvh_.prim_ids; 8-byte size_t in the library, 4-byte also accepted).
+ */
+typedef struct SpkBvhNode {
+    float bounds[6];
+    uint32_t index;
+    uint32_t pad;
+} SpkBvhNode;
+
+typedef struct SpkBvhDesc {
+    const void *nodes;
+    uint32_t num_nodes;
+    uint32_t node_stride;   /* 28 or 32 bytes */
+    const void *prim_ids;
+    uint32_t num_prims;
+    uint32_t prim_id_bytes; /* 4 or 8 */
+} SpkBvhDesc;
+
+/* One per unique io/Mesh.h:7-141 `Mesh` (== one BLAS, MeshRenderProxy.cpp:24-199). Instances share it. */
+typedef struct SpkMeshDesc {
+    const float *vertices;   /* 3*num_vertices, Mesh::vertices */
+    const float *normals;    /* 3*num_vertices, Mesh::normals (required) */
+    const float *tangents;   /* 4*num_vertices, Mesh::tangents (required) */
+    const float *uvs;        /* 2*num_vertices or NULL (Mesh::uvs empty => uv = 0) */
+    const uint32_t *indices; /* 3*num_faces */
+    uint32_t num_vertices;
+    uint32_t num_faces;
+    SpkBvhDesc blas;         /* over faces */
+} SpkMeshDesc;
+
+typedef enum SpkPrimitiveKind { SPK_PRIM_MESH = 0, SPK_PRIM_SPHERE = 1 } SpkPrimitiveKind;
+
+/* One per PrimitiveRenderProxy, in SceneRenderProxy::primitives_ order (== primitive index reported
+ * in SpkHit.prim). fwd/inv are rows 0..2 of Transform::GetMatrix() and of its inverse, bit for bit
+ * (core/math/Transform.h:74-91). Spheres use translation (fwd[3],fwd[7],fwd[11]) and radius2
+ * (SphereRenderProxy.h:33-36). */
+typedef struct SpkPrimitiveDesc {
+    uint32_t kind;     /* SpkPrimitiveKind */
+    uint32_t mesh;     /* index into SpkSceneDesc.meshes (mesh kind) */
+    uint32_t material; /* index into SpkSceneDesc.materials */
+    float radius2;     /* sphere: scaled_radius_2_ */
+    float fwd[12];
+    float inv[12];
+} SpkPrimitiveDesc;
+
+typedef enum SpkMaterialType { SPK_MAT_PBR = 0, SPK_MAT_DIELECTRIC = 1 } SpkMaterialType;
+
+/* io/Material.h:7-22 MaterialResource + Material::Type; 64 bytes like MaterialRenderData
+ * (MaterialRenderProxy.h:39-58). Texture ids index SpkSceneDesc.textures, SPK_INVALID_ID = none. */
+typedef struct SpkMaterialDesc {
+    uint32_t base_color_tex;
+    uint32_t emissive_tex;
+    uint32_t metallic_roughness_tex;
+    uint32_t normal_tex;
+    float metallic;
+    float roughness;
+    float eta;
+    uint32_t type; /* SpkMaterialType */
+    float base_color[3];
+    float pad0;
+    float emissive[3];
+    float pad1;
+} SpkMaterialDesc;
+
+typedef enum SpkPixelFormat {
+    SPK_FMT_RGBA8_UNORM = 0,
+    SPK_FMT_RGBA8_SRGB = 1,
+    SPK_FMT_RGBA16F = 2,
+    SPK_FMT_RGBA32F = 3
+} SpkPixelFormat;
+
+typedef struct SpkTextureDesc {
+    const void *pixels; /* row-major, tightly packed */
+    uint32_t width;
+    uint32_t height;
+    uint32_t format; /* SpkPixelFormat */
+    uint32_t pad;
+} SpkTextureDesc;
+
+/* SkyRenderProxy.cpp:50-64. has_sky==0: no sky light (miss adds nothing). has_map: cube faces in
+ * Image2DCube::FaceId order (+X,-X,+Y,-Y,+Z,-Z). */
+typedef struct SpkSkyDesc {
+    uint32_t has_sky;
+    uint32_t has_map;
+    float color[3];
+    float pad;
+    SpkTextureDesc faces[6];
+} SpkSkyDesc;
+
+typedef struct SpkSceneDesc {
+    uint32_t abi_version;
+    uint32_t num_meshes;
+    const SpkMeshDesc *meshes;
+    uint32_t num_primitives;
+    uint32_t num_materials;
+    const SpkPrimitiveDesc *primitives;
+    const SpkMaterialDesc *materials;
+    uint32_t num_textures;
+    uint32_t pad;
+    const SpkTextureDesc *textures;
+    SpkBvhDesc tlas; /* over primitives (world AABBs), SceneRenderProxy.cpp:31-69 */
+    SpkSkyDesc sky;
+    float world_extent; /* max |coordinate| of the world bounds; sizes the t-culling slack */
+    float pad2;
+} SpkSceneDesc;
+
+/* CameraRenderProxy::{Posture,FocusPlane,Attribute} (CameraRenderProxy.h:31-57). */
+typedef struct SpkCamera {
+    float position[3];
+    float up[3];
+    float front[3];
+    float right[3];
+    float max_u[3];
+    float max_v[3];
+    float lower_left[3];
+    float aperture_radius;
+    float exposure;
+} SpkCamera;
+
+typedef enum SpkAccumMode {
+    SPK_ACCUM_SUM = 0,            /* acc += min(L,limit); resolve divides by the sample count */
+    SPK_ACCUM_RUNNING_AVERAGE = 1 /* acc = lerp(new, acc, N/(N+1)) per sample, CPURenderer.cpp:530-544 */
+} SpkAccumMode;
+
+enum {
+    SPK_FLAG_EXACT_TRAVERSAL = 1u, /* never shorten tmax while traversing (reference behaviour) */
+    SPK_FLAG_COUNTERS = 2u,        /* instrumented kernel: fill node/triangle counters in SpkStats */
+    SPK_FLAG_WAVEFRONT = 4u        /* wavefront (queue) tracer instead of the persistent megakernel */
+};
+
+typedef struct SpkRenderParams {
+    uint32_t first_sample;  /* frame_seed of the first sample, CPURenderer.cpp:432 */
+    uint32_t sample_count;  /* samples per pixel added by this call */
+    uint32_t sample_stride; /* 1; or G when spp is interleaved over G GPUs (this rank: first_sample=g) */
+    uint32_t max_bounce;    /* RenderConfig::max_bounce */
+    float output_limit;     /* CameraRenderProxy::OutputLimit (6) */
+    uint32_t accum_mode;    /* SpkAccumMode */
+    uint32_t flags;
+    uint32_t pad;
+} SpkRenderParams;
+
+/* 32-byte ray, 20-byte hit (IntersectionCandidate, Intersection.h:91-104). */
+typedef struct SpkRay {
+    float origin[3];
+    float pad0;
+    float direction[3];
+    float pad1;
+} SpkRay;
+
+typedef struct SpkHit {
+    float t; /* world t; FLT_MAX when nothing was hit */
+    float u;
+    float v;
+    uint32_t prim; /* primitive index (SceneRenderProxy order) or SPK_INVALID_ID */
+    uint32_t face; /* face index inside the mesh, SPK_INVALID_ID for spheres */
+} SpkHit;
+
+typedef struct SpkStats {
+    uint64_t paths;       /* pixel samples started */
+    uint64_t rays;        /* SceneRenderProxy::Intersect calls (path segments) */
+    uint64_t node_visits; /* inner-node visits (each reads one 64-byte child pair), TLAS + BLAS */
+    uint64_t tri_tests;   /* triangle records fetched and tested */
+    uint64_t inst_visits; /* mesh-instance entries (ray transformed into object space) */
+    uint64_t sphere_tests;
+    double last_ms; /* device time of the last render / trace call (CUDA events on the context stream) */
+    uint64_t kernel_launches; /* kernels launched by this context so far */
+} SpkStats;
+
+typedef enum SpkResolveFormat {
+    SPK_RESOLVE_LINEAR_F32 = 0,  /* W*H float4: mean radiance rgb (pre-tonemap), w = mean valid flag; row j = scene row j */
+    SPK_RESOLVE_TONEMAP_F16 = 1, /* W*H half4, ACES, rows flipped: CPURenderer.cpp:554-576 output_image_ */
+    SPK_RESOLVE_TONEMAP_SRGB8 = 2 /* W*H RGBA8, ACES then pow(0.45) (Utilities.h:411-414), rows flipped */
+} SpkResolveFormat;
+
+typedef struct SpkCreateInfo {
+    uint32_t abi_version;
+    int32_t device; /* CUDA device ordinal */
+    uint32_t width; /* scene resolution */
+    uint32_t height;
+} SpkCreateInfo;
+
+typedef struct SpkContext SpkContext;
+
+const char *spk_cuda_last_error(void);
+uint32_t spk_cuda_abi_version(void);
+
+/* Renderer::CreateRenderer + CudaRenderer::InitRenderResources (Renderer.cpp:17-53). */
+int spk_cuda_create(const SpkCreateInfo *info, SpkContext **out);
+int spk_cuda_destroy(SpkContext *ctx);
+/* Use an externally owned cudaStream_t (e.g. torch's current stream) instead of the context's own. */
+int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream);
+
+/* SceneRenderProxy::Update/UpdateBVH consumer (SceneRenderProxy.cpp:195-297): flattens TLAS/BLAS, triangle,
+ * attribute, material and texture tables into aligned device buffers. Replaces any previous scene. */
+int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *scene);
+/* PrimitiveChangeType::Update (SceneRenderProxy.cpp:212-230): new transforms + rebuilt TLAS, BLAS kept. */
+int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitives, uint32_t num_primitives,
+                              const SpkBvhDesc *tlas);
+/* CameraRenderProxy::OnTransformDirty (CameraRenderProxy.cpp:113-136). */
+int spk_cuda_set_camera(SpkContext *ctx, const SpkCamera *camera);
+/* CPURenderer::Render's NeedClear branch (CPURenderer.cpp:128-137). */
+int spk_cuda_reset_accumulation(SpkContext *ctx);
+/* CPURenderer::BasePass + temporal accumulate (CPURenderer.cpp:419-450, 530-544) for sample_count samples. */
+int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params);
+/* ToneMappingPass + readback (CPURenderer.cpp:554-576; Renderer.cpp:108-180). `total_samples` is the
+ * number of samples summed in the accumulator (all ranks, after the reduce) for SPK_ACCUM_SUM. */
+int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, void *host_out, size_t host_bytes);
+/* Device-resident accumulator (W*H float4) for the NCCL reduce; samples accumulated locally so far. */
+int spk_cuda_accum_device_ptr(SpkContext *ctx, void **device_ptr, size_t *bytes);
+int spk_cuda_accum_sample_count(SpkContext *ctx, uint32_t *count);
+
+/* SceneRenderProxy::Intersect<false> on a ray batch (SceneRenderProxy.cpp:82-126, 299-312), host buffers:
+ * H2D of rays, traversal, D2H of hits inside the call. */
+int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_rays, SpkHit *hits, uint32_t flags);
+/* Same with device-resident buffers (no copies); asynchronous on the context stream. */
+int spk_cuda_trace_closest_device(SpkContext *ctx, const void *d_rays, uint64_t num_rays, void *d_hits,
+                                  uint32_t flags);
+
+int spk_cuda_get_stats(SpkContext *ctx, SpkStats *out);
+int spk_cuda_reset_stats(SpkContext *ctx);
+int spk_cuda_synchronize(SpkContext *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPK_CUDA_H_ */
