@@ -1,0 +1,64 @@
+/* spk_context.h — internal state behind the opaque SpkContext of include/spk_cuda.h (not part of the ABI). */
+#pragma once
+#include "../../include/spk_cuda.h"
+#include "spk_device.cuh"
+
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+
+struct SpkContext
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    uint32_t width = 0, height = 0;
+
+    bool has_scene = false;
+    spk::DScene scene{};
+    std::vector<void *> scene_allocs; // everything the current scene owns on the device
+    // kept for spk_cuda_update_instances
+    std::vector<uint32_t> mesh_root_word;
+    uint32_t tlas_pair_base = 0;
+    uint32_t num_blas_pairs = 0;
+    uint32_t pair_capacity = 0;
+    uint32_t instance_capacity = 0;
+    float4 *d_pairs = nullptr;
+    spk::DInstance *d_instances = nullptr;
+
+    bool has_camera = false;
+    spk::DCamera camera{};
+
+    float4 *d_accum = nullptr; // W*H float4
+    uint32_t accum_samples = 0;
+
+    unsigned long long *d_counters = nullptr; // 8 x u64
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    SpkStats stats{};
+
+    // scratch for the host-buffer ray-batch entry point
+    void *d_rays = nullptr;
+    void *d_hits = nullptr;
+    size_t ray_capacity = 0;
+
+    void *d_resolve = nullptr;
+    size_t resolve_capacity = 0;
+};
+
+namespace spk
+{
+void set_error(const std::string &msg);
+int cuda_fail(cudaError_t e, const char *what);
+#define SPK_CUDA_TRY(expr)                                                                                             \
+    do                                                                                                                 \
+    {                                                                                                                  \
+        cudaError_t e__ = (expr);                                                                                      \
+        if (e__ != cudaSuccess)                                                                                        \
+            return spk::cuda_fail(e__, #expr);                                                                         \
+    } while (0)
+
+// kernels (spk_trace.cu / spk_render.cu)
+int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags);
+int launch_render(SpkContext *ctx, const SpkRenderParams *params);
+int launch_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, uint32_t accum_mode, void *d_out);
+} // namespace spk

@@ -1,0 +1,163 @@
+/*
+ * spk_device.cuh — device-side data layout and the bit-exact arithmetic vocabulary of the `cuda` pipeline.
+ *
+ * Layout in HBM (all arrays 16-byte aligned, built once by spk_cuda_upload_scene, read-only afterwards):
+ *   node pairs   64 B per inner-node visit: the two adjacent children nodes[first_id], nodes[first_id+1] of the
+ *                bvh::v2 layout (core/math/BVH.h:18-19) as 2 x {bounds[6], index, pad}. Because the library places
+ *                children at odd/even ids (1,2),(3,4),.. the device array is nodes[1..] so every pair is 64-B aligned.
+ *                TLAS and all BLAS pair arrays live in ONE buffer; an inner index word is rewritten at upload to the
+ *                absolute pair slot (slot<<4, count 0) so traversal needs no per-mesh base.
+ *   triangles    48 B per triangle, stored in LEAF ORDER (bvh_.prim_ids order) so a leaf is one contiguous run:
+ *                {p0.xyz, face_idx bits}, {e1.xyz, 0}, {e2.xyz, 0} — e1/e2 are the host's floats
+ *                (MeshRenderProxy.cpp:78-92), never recomputed on the device. A leaf index word is rewritten to the
+ *                absolute triangle slot.
+ *   instances    128 B per primitive in TLAS leaf order (SceneRenderProxy.cpp:59-68 permutes primitives_ the same
+ *                way): inv 3x4, fwd 3x4 (bit copies of Transform::GetMatrix of the inverse / forward), root index
+ *                word of the BLAS, kind, radius2, primitive index (SceneRenderProxy order), material, mesh.
+ *
+ * Arithmetic: this header is compiled with -fmad=false. Every reduction mirrors the association the reference's
+ * Eigen expressions compile to with g++ -O2 -ffp-contract=off (re-probed against oracle/_ref):
+ *   a.dot(b)        = (a0*b0 + a1*b1) + a2*b2
+ *   a.squaredNorm() = a0*a0 + (a1*a1 + a2*a2)
+ *   a.normalized()  = a / sqrt(squaredNorm)      (true division)
+ *   M3x3 * v  (row) = m0*v0 + (m1*v1 + m2*v2)    (Transform::TransformDirection)
+ *   Affine * p(row) = ((m0*p0 + m1*p1) + m2*p2) + t   (Transform::TransformPoint)
+ *   cross           = textbook (a1*b2 - a2*b1, ...)
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SPK_INVALID_ID 0xFFFFFFFFu
+#define SPK_FLT_MAX 3.402823466e+38f
+
+namespace spk
+{
+struct __align__(16) DInstance
+{
+    float inv[12]; // rows 0..2 of the inverse transform
+    float fwd[12]; // rows 0..2 of the forward transform
+    uint32_t root; // BLAS root index word (absolute: slot<<4 | count), unused for spheres
+    uint32_t kind; // 0 mesh, 1 sphere
+    float radius2;
+    uint32_t prim; // primitive index in SceneRenderProxy::primitives_ registration order
+    uint32_t material;
+    uint32_t mesh;
+    uint32_t pad[2];
+};
+static_assert(sizeof(DInstance) == 128, "instance record");
+
+struct __align__(16) DMesh
+{
+    const float *normals;    // 3 per vertex
+    const float *tangents;   // 4 per vertex
+    const float *uvs;        // 2 per vertex or nullptr
+    const uint32_t *indices; // 3 per face
+};
+
+struct __align__(16) DMaterial
+{
+    uint32_t base_color_tex, emissive_tex, metallic_roughness_tex, normal_tex;
+    float metallic, roughness, eta;
+    uint32_t type;
+    float base_color[3];
+    float pad0;
+    float emissive[3];
+    float pad1;
+};
+static_assert(sizeof(DMaterial) == 64, "material record");
+
+struct __align__(16) DTexture
+{
+    const void *pixels;
+    uint32_t width, height;
+    uint32_t format; // SpkPixelFormat
+    uint32_t pad;
+};
+
+struct DSky
+{
+    uint32_t has_sky, has_map;
+    float color[3];
+    DTexture faces[6];
+};
+
+struct DCamera
+{
+    float position[3], up[3], front[3], right[3], max_u[3], max_v[3], lower_left[3];
+    float aperture_radius, exposure;
+};
+
+struct DScene
+{
+    const float4 *pairs;        // 4 float4 per pair
+    const float4 *tris;         // 3 float4 per triangle
+    const DInstance *instances; // TLAS leaf order
+    const DMesh *meshes;
+    const DMaterial *materials;
+    const DTexture *textures;
+    uint32_t tlas_root;         // index word of the TLAS root (absolute)
+    uint32_t num_instances;     // 0 => empty scene
+    float cull_extent;          // world extent used for the t-culling slack
+    uint32_t pad;
+    DSky sky;
+};
+
+struct V3
+{
+    float x, y, z;
+};
+
+__device__ __forceinline__ V3 mk(float x, float y, float z)
+{
+    V3 r;
+    r.x = x;
+    r.y = y;
+    r.z = z;
+    return r;
+}
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ V3 cmul(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ float sqnorm(V3 a) { return a.x * a.x + (a.y * a.y + a.z * a.z); }
+__device__ __forceinline__ float norm(V3 a) { return sqrtf(sqnorm(a)); }
+__device__ __forceinline__ V3 normalized(V3 a)
+{
+    float n = sqrtf(sqnorm(a));
+    return mk(a.x / n, a.y / n, a.z / n);
+}
+__device__ __forceinline__ V3 cross(V3 a, V3 b)
+{
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+// Transform::TransformDirection: rows of the 3x3 block, m0*v0 + (m1*v1 + m2*v2)
+__device__ __forceinline__ V3 xform_dir(const float *m, V3 v)
+{
+    return mk(m[0] * v.x + (m[1] * v.y + m[2] * v.z), m[4] * v.x + (m[5] * v.y + m[6] * v.z),
+              m[8] * v.x + (m[9] * v.y + m[10] * v.z));
+}
+// Transform::TransformPoint: ((m0*p0 + m1*p1) + m2*p2) + t
+__device__ __forceinline__ V3 xform_point(const float *m, V3 p)
+{
+    return mk(((m[0] * p.x + m[1] * p.y) + m[2] * p.z) + m[3], ((m[4] * p.x + m[5] * p.y) + m[6] * p.z) + m[7],
+              ((m[8] * p.x + m[9] * p.y) + m[10] * p.z) + m[11]);
+}
+
+// bvh::v2 safe_inverse: 1/x, or copysign(FLT_MAX, x) when |x| <= FLT_EPSILON
+__device__ __forceinline__ float safe_inverse(float x)
+{
+    return fabsf(x) <= 1.1920929e-07f ? copysignf(SPK_FLT_MAX, x) : 1.f / x;
+}
+
+struct Hit
+{
+    float t, u, v;
+    uint32_t inst; // instance slot (TLAS leaf order) or SPK_INVALID_ID
+    uint32_t face;
+};
+} // namespace spk

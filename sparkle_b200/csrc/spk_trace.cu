@@ -1,0 +1,211 @@
+/*
+ * spk_trace.cu — closest-hit traversal of a ray batch: SceneRenderProxy::Intersect<false> per ray
+ * (libraries/source/renderer/proxy/SceneRenderProxy.cpp:82-126, 299-312). Compiled with -fmad=false.
+ *
+ * One thread per ray, 128-thread CTAs. Rays are 32 B (two 128-bit loads), hits 20 B. The node-pair and triangle
+ * arrays are read through the read-only path with 128-bit loads (4 per inner visit, 3 per triangle).
+ * Roofline: HBM/L2-bound pointer chase; algorithmic bytes per ray = 32 + 20 + 64*N_inner + 48*N_tri + 128*N_inst
+ * (SURVEY.md 8d), with the N counted by the COUNT=true instantiation of the same code.
+ */
+#include "spk_context.h"
+#include "spk_traverse.cuh"
+
+namespace spk
+{
+namespace
+{
+constexpr int kTraceThreads = 128;
+
+template <bool CULL, bool COUNT>
+__global__ void __launch_bounds__(kTraceThreads)
+    trace_closest_kernel(const DScene sc, const float4 *__restrict__ rays, uint64_t n, float *__restrict__ hits,
+                         unsigned long long *__restrict__ counters)
+{
+    uint64_t i = uint64_t(blockIdx.x) * kTraceThreads + threadIdx.x;
+    TraceCounters cnt{0, 0, 0, 0};
+    if (i < n)
+    {
+        float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
+        uint32_t stack[64];
+        Hit best;
+        trace_closest<CULL, COUNT>(sc, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), best, stack, cnt);
+        float *o = hits + 5 * i;
+        o[0] = best.t;
+        o[1] = best.u;
+        o[2] = best.v;
+        uint32_t prim = best.inst == SPK_INVALID_ID ? SPK_INVALID_ID : __ldg(&sc.instances[best.inst].prim);
+        o[3] = __uint_as_float(prim);
+        o[4] = __uint_as_float(best.face);
+    }
+    if (COUNT)
+    {
+        // warp-reduce, one atomic per warp and counter
+        uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+        {
+            uint32_t s = __reduce_add_sync(0xffffffffu, v[k]);
+            if ((threadIdx.x & 31) == 0 && s)
+            {
+                atomicAdd(counters + 2 + k, (unsigned long long)s);
+            }
+        }
+    }
+}
+} // namespace
+
+int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags)
+{
+    if (n == 0)
+    {
+        return SPK_OK;
+    }
+    uint64_t blocks = (n + kTraceThreads - 1) / kTraceThreads;
+    if (blocks > 0x7fffffffull)
+    {
+        set_error("spk_cuda_trace_closest: batch too large for one launch");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    bool exact = flags & SPK_FLAG_EXACT_TRAVERSAL, count = flags & SPK_FLAG_COUNTERS;
+    auto *rays = static_cast<const float4 *>(d_rays);
+    auto *hits = static_cast<float *>(d_hits);
+    dim3 grid{unsigned(blocks)}, block{kTraceThreads};
+    if (exact && count)
+        trace_closest_kernel<false, true><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    else if (exact)
+        trace_closest_kernel<false, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    else if (count)
+        trace_closest_kernel<true, true><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    else
+        trace_closest_kernel<true, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    SPK_CUDA_TRY(cudaGetLastError());
+    ctx->stats.kernel_launches++;
+    ctx->stats.rays += n;
+    return SPK_OK;
+}
+} // namespace spk
+
+using namespace spk;
+
+extern "C"
+{
+int spk_cuda_trace_closest_device(SpkContext *ctx, const void *d_rays, uint64_t num_rays, void *d_hits, uint32_t flags)
+{
+    if (!ctx || (num_rays && (!d_rays || !d_hits)))
+    {
+        set_error("spk_cuda_trace_closest_device: null argument");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (!ctx->has_scene)
+    {
+        set_error("spk_cuda_trace_closest: no scene uploaded");
+        return SPK_ERR_NO_SCENE;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = launch_trace_closest(ctx, d_rays, num_rays, d_hits, flags);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
+    return SPK_OK;
+}
+
+int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_rays, SpkHit *hits, uint32_t flags)
+{
+    if (!ctx || (num_rays && (!rays || !hits)))
+    {
+        set_error("spk_cuda_trace_closest: null argument");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (!ctx->has_scene)
+    {
+        set_error("spk_cuda_trace_closest: no scene uploaded");
+        return SPK_ERR_NO_SCENE;
+    }
+    if (num_rays == 0)
+    {
+        return SPK_OK;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    if (num_rays > ctx->ray_capacity)
+    {
+        cudaFree(ctx->d_rays);
+        cudaFree(ctx->d_hits);
+        ctx->d_rays = ctx->d_hits = nullptr;
+        ctx->ray_capacity = 0;
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_rays, num_rays * sizeof(SpkRay)));
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_hits, num_rays * sizeof(SpkHit)));
+        ctx->ray_capacity = num_rays;
+    }
+    SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_rays, rays, num_rays * sizeof(SpkRay), cudaMemcpyHostToDevice, ctx->stream));
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = launch_trace_closest(ctx, ctx->d_rays, num_rays, ctx->d_hits, flags);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
+    SPK_CUDA_TRY(cudaMemcpyAsync(hits, ctx->d_hits, num_rays * sizeof(SpkHit), cudaMemcpyDeviceToHost, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return SPK_OK;
+}
+
+int spk_cuda_get_stats(SpkContext *ctx, SpkStats *out)
+{
+    if (!ctx || !out)
+    {
+        set_error("spk_cuda_get_stats: null argument");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    unsigned long long c[8];
+    SPK_CUDA_TRY(cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+    ctx->stats.paths = c[0];
+    ctx->stats.node_visits = c[2];
+    ctx->stats.tri_tests = c[3];
+    ctx->stats.inst_visits = c[4];
+    ctx->stats.sphere_tests = c[5];
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess)
+    {
+        ctx->stats.last_ms = ms;
+    }
+    else
+    {
+        (void)cudaGetLastError();
+    }
+    *out = ctx->stats;
+    out->rays += c[1]; // path segments the path tracer counted on the device
+    return SPK_OK;
+}
+
+int spk_cuda_reset_stats(SpkContext *ctx)
+{
+    if (!ctx)
+    {
+        set_error("null context");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    uint64_t launches = ctx->stats.kernel_launches;
+    ctx->stats = SpkStats{};
+    ctx->stats.kernel_launches = launches;
+    return SPK_OK;
+}
+
+int spk_cuda_synchronize(SpkContext *ctx)
+{
+    if (!ctx)
+    {
+        set_error("null context");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return SPK_OK;
+}
+} // extern "C"
