@@ -126,6 +126,8 @@ __device__ __forceinline__ void intersect_sphere(const DInstance *__restrict__ i
     if (t > 0.f && t < best.t)
     {
         best.t = t;
+        best.u = 0.f; // SphereRenderProxy::GetIntersection ignores the candidate's u, v (SphereRenderProxy.h:22-31)
+        best.v = 0.f;
         best.inst = inst;
         best.face = SPK_INVALID_ID;
     }

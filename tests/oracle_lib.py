@@ -1,0 +1,102 @@
+"""TEST INFRASTRUCTURE: ctypes loader for the CPU oracle (oracle/oracle.h). Only tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs may import this. kind = "reference" (oracle/_ref/libsparkle_ref.so, the
+reference's own CPU path tracer compiled in place) or "port" (oracle/liboracle.so, the plain C++ restatement)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from sparkle_b200 import _abi as A
+from sparkle_b200.device import HIT_DTYPE
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PATHS = {"reference": os.path.join(ROOT, "oracle", "_ref", "libsparkle_ref.so"),
+         "port": os.path.join(ROOT, "oracle", "liboracle.so")}
+TRACE_BVH_REFERENCE, TRACE_BRUTE_FORCE, TRACE_BVH_CULLED = 0, 1, 2
+
+
+class OrcCounters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("paths", "rays", "node_visits", "tri_tests", "inst_visits", "sphere_tests",
+                                          "rng_draws")]
+
+
+_cache = {}
+
+
+def available(kind):
+    return os.path.exists(PATHS[kind])
+
+
+def load(kind="reference"):
+    if kind in _cache:
+        return _cache[kind]
+    lib = C.CDLL(PATHS[kind])
+    lib.orc_kind.restype = C.c_char_p
+    f32, u32, fp = C.c_float, C.c_uint32, A.fp
+    lib.orc_rng_state.argtypes = [u32, A.u32p]
+    lib.orc_rng_units.argtypes = [u32, u32, fp]
+    lib.orc_kat_vec.argtypes = [u32, fp, fp, fp, fp]
+    lib.orc_kat_libm.argtypes = [u32, f32, f32]
+    lib.orc_kat_libm.restype = f32
+    lib.orc_kat_unit_disk.argtypes = [u32, fp]
+    lib.orc_kat_texture.argtypes = [C.POINTER(A.TextureDesc), f32, f32, fp]
+    lib.orc_kat_sky.argtypes = [C.POINTER(A.SkyDesc), fp, fp]
+    lib.orc_kat_sample_surface.argtypes = [C.POINTER(A.SceneDesc), u32, u32, fp, fp, fp, fp, fp, fp]
+    lib.orc_kat_sample_surface.restype = u32
+    lib.orc_trace_closest.argtypes = [C.POINTER(A.SceneDesc), C.c_void_p, C.c_uint64, C.c_void_p, u32, u32,
+                                      C.POINTER(OrcCounters)]
+    lib.orc_intersect_full.argtypes = [C.POINTER(A.SceneDesc), C.c_void_p, fp]
+    lib.orc_intersect_full.restype = u32
+    lib.orc_render.argtypes = [C.POINTER(A.SceneDesc), C.POINTER(A.Camera), u32, u32, C.POINTER(A.RenderParams), fp,
+                               A.u32p, u32, u32, C.POINTER(OrcCounters)]
+    lib.orc_sample_pixel.argtypes = [C.POINTER(A.SceneDesc), C.POINTER(A.Camera), u32, u32, u32, u32, u32, u32, f32,
+                                     u32, fp, C.POINTER(OrcCounters)]
+    lib.orc_resolve.argtypes = [fp, u32, u32, u32, u32, u32, f32, C.c_void_p]
+    _cache[kind] = lib
+    return lib
+
+
+class Oracle:
+    def __init__(self, kind="reference"):
+        self.lib = load(kind)
+        self.kind = self.lib.orc_kind().decode()
+
+    def trace_closest(self, desc, rays, mode=TRACE_BVH_REFERENCE, threads=8):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.empty(len(rays), HIT_DTYPE)
+        cnt = OrcCounters()
+        rc = self.lib.orc_trace_closest(C.byref(desc), rays.ctypes.data, len(rays), hits.ctypes.data, mode, threads,
+                                        C.byref(cnt))
+        if rc != 0:
+            raise RuntimeError(f"orc_trace_closest -> {rc}")
+        return hits, cnt
+
+    def render(self, desc, cam, width, height, first_sample, sample_count, max_bounce=8, sample_stride=1,
+               accum_mode=A.ACCUM_SUM, accum=None, cumulated=0, threads=8):
+        if accum is None:
+            accum = np.zeros((height, width, 4), np.float32)
+        p = A.RenderParams(first_sample, sample_count, sample_stride, max_bounce, 6.0, accum_mode, 0, 0)
+        cum = C.c_uint32(cumulated)
+        cnt = OrcCounters()
+        rc = self.lib.orc_render(C.byref(desc), C.byref(cam), width, height, C.byref(p), accum.ctypes.data_as(A.fp),
+                                 C.byref(cum), 0, threads, C.byref(cnt))
+        if rc != 0:
+            raise RuntimeError(f"orc_render -> {rc}")
+        return accum, cum.value
+
+    def sample_pixel(self, desc, cam, width, height, i, j, frame_seed, max_bounce=8):
+        out = np.zeros(8, np.float32)
+        rc = self.lib.orc_sample_pixel(C.byref(desc), C.byref(cam), width, height, i, j, frame_seed, max_bounce, 6.0,
+                                       0, out.ctypes.data_as(A.fp), None)
+        if rc != 0:
+            raise RuntimeError(f"orc_sample_pixel -> {rc}")
+        return out
+
+    def resolve(self, accum, fmt, total_samples, exposure=1.0, accum_mode=A.ACCUM_SUM):
+        h, w = accum.shape[:2]
+        out = np.empty((h, w, 4), np.float32 if fmt == A.RESOLVE_LINEAR_F32 else np.float16)
+        rc = self.lib.orc_resolve(np.ascontiguousarray(accum).ctypes.data_as(A.fp), w, h, accum_mode, fmt,
+                                  total_samples, exposure, out.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"orc_resolve -> {rc}")
+        return out
