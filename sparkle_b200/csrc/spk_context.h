@@ -31,6 +31,7 @@ struct SpkContext
 
     float4 *d_accum = nullptr; // W*H float4
     uint32_t accum_samples = 0;
+    uint32_t accum_mode = 0; // SpkAccumMode of the samples in d_accum
 
     unsigned long long *d_counters = nullptr; // 8 x u64
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

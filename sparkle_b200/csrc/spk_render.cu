@@ -1,16 +1,314 @@
-/* spk_render.cu — placeholder until the path tracer lands (next commit). */
+/*
+ * spk_render.cu — the path tracer (persistent-thread megakernel form) and the resolve (tone-mapping) pass.
+ *
+ *   CPURenderer::BasePass     libraries/source/renderer/renderer/CPURenderer.cpp:419-450  per-pixel reseed, one task per row
+ *   CPURenderer::RenderPixel  :398-417   jitter (2 draws), SamplePixel, clamp to OutputLimit, (rgb, valid) out
+ *   SetupViewRay              :220-238   thin lens, UnitDisk always drawn
+ *   SamplePixel               :240-396   bounce loop, sky on miss, emissive stop, early-out, Russian roulette from bounce 3
+ *   DenoisePass (temporal)    :530-544   acc = lerp(new, acc, N/(N+spp))
+ *   ToneMappingPass/ACESFilm  :554-576
+ *
+ * Work decomposition: one thread owns one pixel and loops over the samples of this call, keeping the pixel's
+ * accumulator in registers (one 16-byte read-modify-write of the accumulation buffer per pixel per call, not per
+ * sample). A warp covers an 8x4 pixel tile so primary rays stay coherent. Sample s of pixel p depends only on (p, s)
+ * through its seed, so any split of the sample range over launches or GPUs gives the same sum.
+ * Compiled with -fmad=false (spk_device.cuh).
+ */
 #include "spk_context.h"
+#include "spk_shade.cuh"
+#include "spk_traverse.cuh"
+
+namespace spk
+{
+namespace
+{
+constexpr int kTileW = 8, kTileH = 4; // one warp
+constexpr int kWarpsPerBlock = 4;
+
+struct RenderArgs
+{
+    uint32_t width, height;
+    uint32_t first_sample, sample_count, sample_stride, max_bounce;
+    float output_limit;
+    uint32_t accum_mode;
+    uint32_t debug;
+    uint32_t cumulated; // samples already in the accumulator (running-average mode)
+};
+
+template <bool CULL>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+    render_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
+                  unsigned long long *__restrict__ counters)
+{
+    const uint32_t tiles_x = (a.width + kTileW - 1) / kTileW;
+    const uint32_t warp = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t i = (warp % tiles_x) * kTileW + (lane & (kTileW - 1));
+    const uint32_t j = (warp / tiles_x) * kTileH + (lane / kTileW);
+    uint32_t rays = 0;
+    if (i < a.width && j < a.height)
+    {
+        const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
+        const V3 cpos = mk(cam.position[0], cam.position[1], cam.position[2]);
+        const V3 cup = mk(cam.up[0], cam.up[1], cam.up[2]);
+        const V3 cright = mk(cam.right[0], cam.right[1], cam.right[2]);
+        const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
+        const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
+        const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
+        float4 acc = accum[size_t(j) * a.width + i];
+        uint32_t stack[64];
+        TraceCounters cnt{0, 0, 0, 0};
+        for (uint32_t s = 0; s < a.sample_count; s++)
+        {
+            // CPURenderer.cpp:442-443, unsigned wrap
+            const uint32_t frame_seed = a.first_sample + s * a.sample_stride;
+            Rng rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+            float u = ((float)i + rng_unit(rng)) * pw;
+            float v = ((float)j + rng_unit(rng)) * ph;
+            // SetupViewRay
+            float dx, dy;
+            unit_disk(rng, dx, dy);
+            dx = dx * cam.aperture_radius;
+            dy = dy * cam.aperture_radius;
+            V3 origin = cpos + (dx * cright + dy * cup);
+            V3 target = lower_left + u * max_u + v * max_v;
+            V3 dir = normalized(target - origin);
+
+            V3 throughput = mk(1.f, 1.f, 1.f), color = mk(0.f, 0.f, 0.f);
+            float valid = 1.f;
+            for (uint32_t bounce = 0; bounce < a.max_bounce; bounce++)
+            {
+                Hit hit;
+                trace_closest<CULL, false>(sc, origin, dir, hit, stack, cnt);
+                rays++;
+                if (hit.inst == SPK_INVALID_ID)
+                {
+                    if (sc.sky.has_sky)
+                    {
+                        color = color + cmul(sky_evaluate(sc, dir), throughput);
+                    }
+                    break;
+                }
+                Surface sf;
+                get_intersection(sc, origin, dir, hit, sf);
+                if (a.debug)
+                {
+                    // parity probes (tests only): first-hit normal / tangent / (u, v, t)
+                    color = a.debug == 1 ? sf.normal : a.debug == 2 ? sf.tangent : mk(sf.u, sf.v, hit.t);
+                    break;
+                }
+                V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
+                if (norm(emissive) > kEps)
+                {
+                    color = color + cmul(emissive, throughput);
+                    break;
+                }
+                V3 next_dir;
+                V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
+                throughput = cmul(throughput, this_throughput);
+                if (sqnorm(throughput) < kEps)
+                {
+                    valid = -1.f;
+                    break;
+                }
+                if (bounce >= 3)
+                {
+                    float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
+                    p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
+                    if (rng_unit(rng) > p)
+                    {
+                        break;
+                    }
+                    throughput = throughput / p;
+                }
+                origin = sf.location + next_dir * kTolerance;
+                dir = next_dir;
+            }
+            color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
+            if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
+            {
+                uint32_t n = a.cumulated + s;
+                float ma = (float)n / (float)(n + 1u);
+                acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
+                                  lerp1(valid, acc.w, ma));
+            }
+            else
+            {
+                acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
+            }
+        }
+        accum[size_t(j) * a.width + i] = acc;
+    }
+    uint32_t total = __reduce_add_sync(0xffffffffu, rays);
+    uint32_t pixels = __popc(__ballot_sync(0xffffffffu, i < a.width && j < a.height));
+    if (lane == 0 && pixels)
+    {
+        atomicAdd(counters + 0, (unsigned long long)pixels * a.sample_count);
+        atomicAdd(counters + 1, (unsigned long long)total);
+    }
+}
+
+__device__ __forceinline__ float aces(float c)
+{
+    // ACESFilm (CPURenderer.cpp:554-563): clamp((c(2.51c+0.03))/(c(2.43c+0.59)+0.14), 0, 1)
+    float r = (c * (c * 2.51f + 0.03f)) / (c * (c * 2.43f + 0.59f) + 0.14f);
+    return fminf(fmaxf(r, 0.f), 1.f);
+}
+
+__global__ void resolve_kernel(const float4 *__restrict__ accum, uint32_t width, uint32_t height, uint32_t format,
+                               float divisor, float exposure, void *__restrict__ out)
+{
+    uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= width * height)
+    {
+        return;
+    }
+    uint32_t i = idx % width, j = idx / width;
+    float4 p = accum[idx];
+    if (divisor != 1.f)
+    {
+        p = make_float4(p.x / divisor, p.y / divisor, p.z / divisor, p.w / divisor);
+    }
+    if (format == SPK_RESOLVE_LINEAR_F32)
+    {
+        static_cast<float4 *>(out)[idx] = p;
+        return;
+    }
+    float r = aces(p.x * exposure), g = aces(p.y * exposure), b = aces(p.z * exposure);
+    size_t o = size_t(height - 1 - j) * width + i; // image.SetPixel(i, H-1-j, ...)
+    if (format == SPK_RESOLVE_TONEMAP_F16)
+    {
+        __half2 lo = __floats2half2_rn(r, g), hi = __floats2half2_rn(b, 1.f);
+        uint2 raw;
+        raw.x = *reinterpret_cast<uint32_t *>(&lo);
+        raw.y = *reinterpret_cast<uint32_t *>(&hi);
+        static_cast<uint2 *>(out)[o] = raw;
+    }
+    else
+    {
+        // Image2D::SetPixel on an sRGB8 image: LinearToSrgb = pow(0.45), VecToColor = (v*255) truncated
+        uchar4 c;
+        c.x = (unsigned char)(ref_pow(r, 0.45f) * 255.f);
+        c.y = (unsigned char)(ref_pow(g, 0.45f) * 255.f);
+        c.z = (unsigned char)(ref_pow(b, 0.45f) * 255.f);
+        c.w = 255;
+        static_cast<uchar4 *>(out)[o] = c;
+    }
+}
+} // namespace
+
+int launch_render(SpkContext *ctx, const SpkRenderParams *p)
+{
+    RenderArgs a;
+    a.width = ctx->width;
+    a.height = ctx->height;
+    a.first_sample = p->first_sample;
+    a.sample_count = p->sample_count;
+    a.sample_stride = p->sample_stride ? p->sample_stride : 1u;
+    a.max_bounce = p->max_bounce;
+    a.output_limit = p->output_limit;
+    a.accum_mode = p->accum_mode;
+    a.cumulated = ctx->accum_samples;
+    a.debug = (p->flags >> 8) & 3u;
+    uint32_t tiles = ((a.width + kTileW - 1) / kTileW) * ((a.height + kTileH - 1) / kTileH);
+    dim3 grid{(tiles + kWarpsPerBlock - 1) / kWarpsPerBlock}, block{kWarpsPerBlock * 32};
+    const DScene &scene = ctx->scene;
+    if (p->flags & SPK_FLAG_EXACT_TRAVERSAL)
+        render_kernel<false><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters);
+    else
+        render_kernel<true><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters);
+    SPK_CUDA_TRY(cudaGetLastError());
+    ctx->stats.kernel_launches++;
+    return SPK_OK;
+}
+} // namespace spk
+
 using namespace spk;
+
 extern "C"
 {
-int spk_cuda_render(SpkContext *, const SpkRenderParams *)
+int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params)
 {
-    set_error("spk_cuda_render: not built yet");
-    return SPK_ERR_UNSUPPORTED;
+    if (!ctx || !params)
+    {
+        set_error("spk_cuda_render: null argument");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (!ctx->has_scene)
+    {
+        set_error("spk_cuda_render: no scene uploaded");
+        return SPK_ERR_NO_SCENE;
+    }
+    if (!ctx->has_camera)
+    {
+        set_error("spk_cuda_render: no camera set");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (params->accum_mode > SPK_ACCUM_RUNNING_AVERAGE || !(params->output_limit > 0.f))
+    {
+        set_error("spk_cuda_render: bad accum_mode or output_limit");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (params->flags & SPK_FLAG_WAVEFRONT)
+    {
+        set_error("spk_cuda_render: the wavefront tracer is not built; the megakernel is the measured choice");
+        return SPK_ERR_UNSUPPORTED;
+    }
+    if (ctx->accum_samples != 0 && params->accum_mode != ctx->accum_mode)
+    {
+        set_error("spk_cuda_render: accum_mode changed without spk_cuda_reset_accumulation");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (params->sample_count == 0)
+    {
+        return SPK_OK;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = launch_render(ctx, params);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->accum_mode = params->accum_mode;
+    ctx->accum_samples += params->sample_count;
+    return SPK_OK;
 }
-int spk_cuda_resolve(SpkContext *, uint32_t, uint32_t, void *, size_t)
+
+int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, void *host_out, size_t host_bytes)
 {
-    set_error("spk_cuda_resolve: not built yet");
-    return SPK_ERR_UNSUPPORTED;
+    if (!ctx || !host_out || format > SPK_RESOLVE_TONEMAP_SRGB8)
+    {
+        set_error("spk_cuda_resolve: null argument or unknown format");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    size_t pixels = size_t(ctx->width) * ctx->height;
+    size_t need = pixels * (format == SPK_RESOLVE_LINEAR_F32 ? 16 : format == SPK_RESOLVE_TONEMAP_F16 ? 8 : 4);
+    if (host_bytes < need)
+    {
+        set_error("spk_cuda_resolve: host buffer too small");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    if (ctx->resolve_capacity < need)
+    {
+        cudaFree(ctx->d_resolve);
+        ctx->d_resolve = nullptr;
+        ctx->resolve_capacity = 0;
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_resolve, need));
+        ctx->resolve_capacity = need;
+    }
+    uint32_t n = total_samples ? total_samples : ctx->accum_samples;
+    float divisor = ctx->accum_mode == SPK_ACCUM_SUM ? (float)(n ? n : 1u) : 1.f;
+    float exposure = ctx->has_camera ? ctx->camera.exposure : 1.f;
+    unsigned blocks = unsigned((pixels + 255) / 256);
+    resolve_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->d_accum, ctx->width, ctx->height, format, divisor, exposure,
+                                                    ctx->d_resolve);
+    SPK_CUDA_TRY(cudaGetLastError());
+    ctx->stats.kernel_launches++;
+    SPK_CUDA_TRY(cudaMemcpyAsync(host_out, ctx->d_resolve, need, cudaMemcpyDeviceToHost, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return SPK_OK;
 }
-}
+} // extern "C"

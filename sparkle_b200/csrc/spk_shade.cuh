@@ -1,0 +1,462 @@
+/*
+ * spk_shade.cuh — per-(pixel,sample) RNG, hit attributes, materials, BxDF sampling and the sky, operation for operation
+ * as the reference CPU path tracer evaluates them. Compiled with -fmad=false.
+ *
+ *   RNG            core/math/Sampler.h:16-53, thirdparty/xoshiro_cpp/XoshiroCpp.hpp (Xoshiro128Plus, SplitMix64)
+ *   hit attributes MeshRenderProxy::GetIntersection (MeshRenderProxy.cpp:340-361), io/Mesh.h:86-134,
+ *                  SphereRenderProxy::GetIntersection (SphereRenderProxy.h:22-31)
+ *   textures       Image2D::Sample (io/Image.h:112-152), utilities::SRGBtoLinear (Utilities.h:416-425)
+ *   materials      MaterialRenderProxy.h:117-162, PbrMaterialRenderProxy.h:15-51, DialetricMaterialRenderProxy.h:16-38
+ *   BxDFs          scene/material/BxDF.h:32-141, DistributionVn (Sampler.h:133-165), Utilities.h:201-324,434-451
+ *   sky            SkyRenderProxy::Evaluate (SkyRenderProxy.cpp:50-64), Image2DCube (io/Image.cpp:298-357)
+ *
+ * libm: sqrt and division are IEEE on the device. sin, cos and pow are evaluated in double and rounded once to float;
+ * glibc's float routines are within 0.56 ulp, so the two agree except for 1.3 % (sin, cos) / 0.07 % (pow) of arguments
+ * where they differ by one ulp (measured against the box's libm). A one-ulp difference moves a path
+ * continuously (~1e-7 relative); only a random number within an ulp of a branch threshold changes a decision.
+ */
+#pragma once
+#include "spk_device.cuh"
+
+#include <cuda_fp16.h>
+
+namespace spk
+{
+constexpr float kEps = 1e-6f;
+constexpr float kTolerance = 1e-4f;
+constexpr float kPi = 3.14159274101257324f;      // std::numbers::pi_v<float>
+constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<float>
+
+__device__ __forceinline__ float ref_sin(float x) { return (float)sin((double)x); }
+__device__ __forceinline__ float ref_cos(float x) { return (float)cos((double)x); }
+__device__ __forceinline__ float ref_pow(float x, float y) { return (float)pow((double)x, (double)y); }
+// std::pow(x, 5.f): exact product in double, one rounding
+__device__ __forceinline__ float ref_pow5(float x)
+{
+    double d = (double)x, d2 = d * d;
+    return (float)(d2 * d2 * d);
+}
+
+// ---- XoshiroCpp::Xoshiro128Plus seeded through SplitMix64, sampler::RandomUnit ----
+struct Rng
+{
+    uint32_t s0, s1, s2, s3;
+};
+
+__device__ __forceinline__ uint32_t splitmix_next(unsigned long long &x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    unsigned long long z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return (uint32_t)(z ^ (z >> 31));
+}
+
+__device__ __forceinline__ Rng rng_seed(uint32_t seed)
+{
+    unsigned long long x = seed;
+    Rng r;
+    r.s0 = splitmix_next(x);
+    r.s1 = splitmix_next(x);
+    r.s2 = splitmix_next(x);
+    r.s3 = splitmix_next(x);
+    return r;
+}
+
+__device__ __forceinline__ float rng_unit(Rng &r)
+{
+    uint32_t result = r.s0 + r.s3;
+    uint32_t t = r.s1 << 9;
+    r.s2 ^= r.s0;
+    r.s3 ^= r.s1;
+    r.s1 ^= r.s2;
+    r.s0 ^= r.s3;
+    r.s2 ^= t;
+    r.s3 = (r.s3 << 11) | (r.s3 >> 21);
+    // static_cast<float>(r) / static_cast<float>(UINT32_MAX): both round to nearest; 1.0f is reachable
+    return __uint2float_rn(result) / 4294967296.0f;
+}
+
+// sampler::UnitDisk: rand, then theta = (u * 2.0f) * Pi
+__device__ __forceinline__ void unit_disk(Rng &r, float &x, float &y)
+{
+    float rand = rng_unit(r);
+    float theta = rng_unit(r) * 2.0f * kPi;
+    float rad = sqrtf(rand);
+    x = rad * ref_cos(theta);
+    y = rad * ref_sin(theta);
+}
+
+// ---- textures: Image2D::Sample ----
+__device__ __forceinline__ uint32_t wrap_mod(int a, uint32_t b)
+{
+    return ((uint32_t)(a % (int)b) + b) % b;
+}
+
+__device__ __forceinline__ float4 access_pixel(const DTexture &t, uint32_t x, uint32_t y)
+{
+    size_t idx = size_t(y) * t.width + x;
+    if (t.format <= 1u) // RGBA8 unorm / srgb: ColorToVec = cast<float>() / 255.f
+    {
+        uchar4 c = __ldg(reinterpret_cast<const uchar4 *>(t.pixels) + idx);
+        return make_float4((float)c.x / 255.f, (float)c.y / 255.f, (float)c.z / 255.f, (float)c.w / 255.f);
+    }
+    if (t.format == 2u) // RGBAFloat16
+    {
+        uint2 raw = __ldg(reinterpret_cast<const uint2 *>(t.pixels) + idx);
+        __half2 a = *reinterpret_cast<__half2 *>(&raw.x), b = *reinterpret_cast<__half2 *>(&raw.y);
+        float2 fa = __half22float2(a), fb = __half22float2(b);
+        return make_float4(fa.x, fa.y, fb.x, fb.y);
+    }
+    return __ldg(reinterpret_cast<const float4 *>(t.pixels) + idx);
+}
+
+__device__ __forceinline__ float lerp1(float a, float b, float f) { return a + (b - a) * f; }
+
+__device__ __forceinline__ float srgb_to_linear(float c)
+{
+    float cutoff = c < 0.04045f ? 1.f : 0.f;
+    float higher = ref_pow((c + 0.055f) / 1.055f, 2.4f);
+    float lower = c / 12.92f;
+    return higher * (1.f - cutoff) + lower * cutoff;
+}
+
+__device__ __forceinline__ V3 sample_texture(const DTexture &t, float u, float v)
+{
+    float px = u * (float)(t.width - 1), py = v * (float)(t.height - 1);
+    int ui = (int)px, vi = (int)py; // utilities::Decompose: truncation toward zero
+    float uc = px - (float)ui, vc = py - (float)vi;
+    uint32_t x0 = wrap_mod(ui, t.width), x1 = wrap_mod(ui + 1, t.width);
+    uint32_t y0 = wrap_mod(vi, t.height), y1 = wrap_mod(vi + 1, t.height);
+    float4 s00 = access_pixel(t, x0, y0), s10 = access_pixel(t, x1, y0);
+    float4 s01 = access_pixel(t, x0, y1), s11 = access_pixel(t, x1, y1);
+    float r0 = lerp1(s00.x, s10.x, uc), g0 = lerp1(s00.y, s10.y, uc), b0 = lerp1(s00.z, s10.z, uc);
+    float r1 = lerp1(s01.x, s11.x, uc), g1 = lerp1(s01.y, s11.y, uc), b1 = lerp1(s01.z, s11.z, uc);
+    V3 c = mk(lerp1(r0, r1, vc), lerp1(g0, g1, vc), lerp1(b0, b1, vc));
+    if (t.format == 1u) // pseudo sRGB decode after filtering
+    {
+        c = mk(srgb_to_linear(c.x), srgb_to_linear(c.y), srgb_to_linear(c.z));
+    }
+    return c;
+}
+
+// utilities::GetPossibleMajorAxis
+__device__ __forceinline__ V3 major_axis(V3 n)
+{
+    if (fabsf(n.x) < kInvSqrt3)
+    {
+        return mk(1.f, 0.f, 0.f);
+    }
+    if (fabsf(n.y) < kInvSqrt3)
+    {
+        return mk(0.f, 1.f, 0.f);
+    }
+    return mk(0.f, 0.f, 1.f);
+}
+
+// ---- hit attributes: {Mesh,Sphere}RenderProxy::GetIntersection ----
+struct Surface
+{
+    V3 location, normal, tangent;
+    float u, v; // texture coordinate
+    uint32_t material;
+};
+
+template <typename T> __device__ __forceinline__ float bary(T v0, T v1, T v2, float u, float v)
+{
+    return v0 + (v1 - v0) * u + (v2 - v0) * v; // utilities::Lerp(v0, v1, v2, u, v)
+}
+
+__device__ __forceinline__ void material_normal_texture(const DScene &sc, const DMaterial &m, float tu, float tv,
+                                                        V3 tangent, float headedness, V3 &n)
+{
+    // MaterialRenderProxy::GetNormal = Sample(uv) * 2 - Ones; utilities::TangentSpaceToWorldSpace
+    V3 s = sample_texture(sc.textures[m.normal_tex], tu, tv);
+    V3 tn = mk(s.x * 2.f - 1.f, s.y * 2.f - 1.f, s.z * 2.f - 1.f);
+    // NB `auto bi_tangent = ...` (Utilities.h:403-409) is an Eigen expression over a temporary: undefined behaviour in
+    // the reference. This follows what the source says; the oracle TU is built so that it does too (oracle/Makefile).
+    V3 bi = cross(n, tangent) * headedness;
+    n = normalized(mk(tangent.x * tn.x + bi.x * tn.y + n.x * tn.z, tangent.y * tn.x + bi.y * tn.y + n.y * tn.z,
+                      tangent.z * tn.x + bi.z * tn.y + n.z * tn.z));
+}
+
+__device__ __forceinline__ void get_intersection(const DScene &sc, V3 wo, V3 wd, const Hit &hit, Surface &sf)
+{
+    const DInstance *__restrict__ in = sc.instances + hit.inst;
+    sf.material = __ldg(&in->material);
+    sf.location = wo + wd * hit.t; // Intersection::Update -> Ray::At(t)
+    if (__ldg(&in->kind) == 1u)
+    {
+        V3 center = mk(__ldg(&in->fwd[3]), __ldg(&in->fwd[7]), __ldg(&in->fwd[11]));
+        V3 p = wo + wd * hit.t;
+        sf.normal = normalized(p - center);
+        sf.tangent = major_axis(sf.normal);
+        sf.u = 0.f;
+        sf.v = 0.f;
+        return;
+    }
+    const DMesh &mesh = sc.meshes[__ldg(&in->mesh)];
+    const uint32_t *idx = mesh.indices + size_t(hit.face) * 3;
+    uint32_t i0 = __ldg(idx), i1 = __ldg(idx + 1), i2 = __ldg(idx + 2);
+    float u = hit.u, v = hit.v;
+    if (mesh.uvs)
+    {
+        const float2 *t = reinterpret_cast<const float2 *>(mesh.uvs);
+        float2 t0 = __ldg(t + i0), t1 = __ldg(t + i1), t2 = __ldg(t + i2);
+        sf.u = bary(t0.x, t1.x, t2.x, u, v);
+        sf.v = bary(t0.y, t1.y, t2.y, u, v);
+    }
+    else
+    {
+        sf.u = 0.f;
+        sf.v = 0.f;
+    }
+    const float *nn = mesh.normals;
+    V3 n = mk(bary(__ldg(nn + 3 * i0), __ldg(nn + 3 * i1), __ldg(nn + 3 * i2), u, v),
+              bary(__ldg(nn + 3 * i0 + 1), __ldg(nn + 3 * i1 + 1), __ldg(nn + 3 * i2 + 1), u, v),
+              bary(__ldg(nn + 3 * i0 + 2), __ldg(nn + 3 * i1 + 2), __ldg(nn + 3 * i2 + 2), u, v));
+    const float4 *tt = reinterpret_cast<const float4 *>(mesh.tangents);
+    float4 g0 = __ldg(tt + i0), g1 = __ldg(tt + i1), g2 = __ldg(tt + i2);
+    V3 tg = mk(bary(g0.x, g1.x, g2.x, u, v), bary(g0.y, g1.y, g2.y, u, v), bary(g0.z, g1.z, g2.z, u, v));
+    float tw = bary(g0.w, g1.w, g2.w, u, v);
+    const DMaterial &m = sc.materials[sf.material];
+    if (__ldg(&m.normal_tex) != SPK_INVALID_ID)
+    {
+        material_normal_texture(sc, m, sf.u, sf.v, tg, tw, n);
+    }
+    // inv_transform.TransformDirectionTangentSpace = the FORWARD 3x3 block (Transform.h:105-108 on the inverse)
+    float fwd[12];
+    const float4 *mm = reinterpret_cast<const float4 *>(in) + 3;
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        float4 a = __ldg(mm + k);
+        fwd[4 * k] = a.x;
+        fwd[4 * k + 1] = a.y;
+        fwd[4 * k + 2] = a.z;
+        fwd[4 * k + 3] = a.w;
+    }
+    sf.normal = normalized(xform_dir(fwd, n));
+    sf.tangent = xform_dir(fwd, tg);
+}
+
+// ---- MaterialRenderProxy getters ----
+struct MaterialSample
+{
+    V3 base_color;
+    float roughness, metallic;
+};
+
+__device__ __forceinline__ V3 material_emissive(const DScene &sc, const DMaterial &m, float u, float v)
+{
+    V3 e = mk(__ldg(&m.emissive[0]), __ldg(&m.emissive[1]), __ldg(&m.emissive[2]));
+    uint32_t tex = __ldg(&m.emissive_tex);
+    if (tex != SPK_INVALID_ID)
+    {
+        e = cmul(sample_texture(sc.textures[tex], u, v), e);
+    }
+    return e;
+}
+
+__device__ __forceinline__ MaterialSample material_sample(const DScene &sc, const DMaterial &m, float u, float v)
+{
+    MaterialSample s;
+    s.base_color = mk(__ldg(&m.base_color[0]), __ldg(&m.base_color[1]), __ldg(&m.base_color[2]));
+    s.roughness = __ldg(&m.roughness);
+    s.metallic = __ldg(&m.metallic);
+    uint32_t bt = __ldg(&m.base_color_tex), mt = __ldg(&m.metallic_roughness_tex);
+    if (bt != SPK_INVALID_ID)
+    {
+        s.base_color = cmul(sample_texture(sc.textures[bt], u, v), s.base_color);
+    }
+    if (mt != SPK_INVALID_ID)
+    {
+        V3 mr = sample_texture(sc.textures[mt], u, v);
+        s.roughness = mr.y * s.roughness;
+        s.metallic = mr.z * s.metallic;
+    }
+    return s;
+}
+
+// ---- BxDF helpers (Utilities.h) ----
+__device__ __forceinline__ float schlick1(float cos_i, float r0) { return r0 + (1.f - r0) * ref_pow5(1.f - cos_i); }
+
+__device__ __forceinline__ float smith_ggx_correlated(float cos_o, float cos_i, float roughness)
+{
+    float a = roughness * roughness, a2 = a * a;
+    float ggx_i = cos_o * sqrtf((-cos_i * a2 + cos_i) * cos_i + a2);
+    float ggx_o = cos_i * sqrtf((-cos_o * a2 + cos_o) * cos_o + a2);
+    return 2.f * cos_o * cos_i / (ggx_o + ggx_i);
+}
+
+__device__ __forceinline__ float geometry_schlick_ggx(float cos_theta, float roughness)
+{
+    float a = roughness * roughness, a2 = a * a;
+    float tan2 = (1.f - cos_theta * cos_theta) / (cos_theta * cos_theta);
+    return 2.f / (1.f + sqrtf(1.f + a2 * tan2));
+}
+
+// sampler::DistributionVn::Sample (Sampler.h:133-165)
+__device__ __forceinline__ V3 sample_vndf(Rng &rng, V3 wo, float roughness)
+{
+    float a = roughness * roughness;
+    float u1 = rng_unit(rng), u2 = rng_unit(rng);
+    V3 v = normalized(mk(wo.x * a, wo.y * a, wo.z));
+    V3 t1 = v.z < 0.999f ? normalized(cross(v, mk(0.f, 0.f, 1.f))) : mk(1.f, 0.f, 0.f);
+    V3 t2 = cross(v, t1);
+    float r = sqrtf(u1);
+    float phi = 2.f * kPi * u2;
+    float p1 = r * ref_cos(phi), p2 = r * ref_sin(phi);
+    float s = 0.5f * (1.f + v.z);
+    p2 = (1.f - s) * sqrtf(1.f - p1 * p1) + s * p2;
+    float c = sqrtf(fmaxf(0.f, 1.f - p1 * p1 - p2 * p2));
+    V3 n = mk(p1 * t1.x + p2 * t2.x + c * v.x, p1 * t1.y + p2 * t2.y + c * v.y, p1 * t1.z + p2 * t2.z + c * v.z);
+    return normalized(mk(a * n.x, a * n.y, fmaxf(0.f, n.z)));
+}
+
+// utilities::GetLocalAxisFromNormal(normal, major_axis = tangent)
+__device__ __forceinline__ void local_axes(V3 normal, V3 tangent, V3 &u, V3 &v, V3 &w)
+{
+    u = normalized(cross(normal, tangent));
+    v = cross(normal, u);
+    w = normal;
+}
+
+// MaterialRenderProxy::SampleSurface for Pbr / Dielectric; returns this bounce's throughput, sets wi (world)
+__device__ __forceinline__ V3 sample_surface(const DScene &sc, Rng &rng, const Surface &sf, V3 ray_dir, V3 &wi_world)
+{
+    const DMaterial &m = sc.materials[sf.material];
+    MaterialSample ms = material_sample(sc, m, sf.u, sf.v);
+    V3 au, av, aw;
+    local_axes(sf.normal, sf.tangent, au, av, aw);
+    V3 w_o = -ray_dir;
+    V3 lwo = mk(dot(w_o, au), dot(w_o, av), dot(w_o, aw)); // TransformBasisToLocal
+    V3 lwi = mk(0.f, 0.f, 0.f);
+    V3 throughput;
+    if (__ldg(&m.type) == 1u)
+    {
+        // DieletricBxDF::Sample (BxDF.h:112-141), FrDielectric (Utilities.h:301-324), EtaI = 1
+        float eta = __ldg(&m.eta);
+        float cos_i = lwo.z, eta_i = 1.f, eta_t = eta;
+        if (!(cos_i > 0.f))
+        {
+            eta_i = eta;
+            eta_t = 1.f;
+            cos_i = -cos_i;
+        }
+        float sin_i = sqrtf(1.f - cos_i * cos_i);
+        float ref_idx = eta_i / eta_t;
+        float sin_t = ref_idx * sin_i;
+        float fresnel;
+        if (sin_t >= 1.f)
+        {
+            fresnel = 1.f;
+        }
+        else
+        {
+            float r0 = (1.f - ref_idx) / (1.f + ref_idx);
+            r0 = r0 * r0;
+            fresnel = schlick1(cos_i, r0);
+        }
+        if (rng_unit(rng) < fresnel)
+        {
+            lwi = mk(-lwo.x, -lwo.y, lwo.z); // utilities::Reflect(w)
+        }
+        else
+        {
+            bool entering = lwo.z > 0.f;
+            float ratio = entering ? 1.f / eta : eta / 1.f;
+            // utilities::Refract
+            float ct = lwo.z;
+            float sin_i2 = 1.f - ct * ct;
+            float sin_t2 = ratio * ratio * sin_i2;
+            float cos_t = sqrtf(1.f - sin_t2) * (ct > 0.f ? -1.f : 1.f);
+            lwi = normalized(mk(-ratio * lwo.x, -ratio * lwo.y, cos_t));
+        }
+        throughput = ms.base_color;
+    }
+    else
+    {
+        // SpecularBxDF::Sample (BxDF.h:47-110)
+        V3 wm = sample_vndf(rng, lwo, ms.roughness);
+        float k = dot(lwo, wm) * 2.f;
+        V3 swi = mk(wm.x * k - lwo.x, wm.y * k - lwo.y, wm.z * k - lwo.z); // utilities::Reflect(w_o, w_m)
+        float cos_o = fmaxf(fabsf(lwo.z), 0.f), cos_in = fmaxf(fabsf(swi.z), 0.f), cos_m = fmaxf(fabsf(wm.z), 0.f);
+        float local_cos_i = dot(swi, wm);
+        bool valid = false;
+        V3 fresnel_color = mk(0.f, 0.f, 0.f);
+        if (cos_o > kEps && cos_in > kEps && cos_m > kEps)
+        {
+            if (rng_unit(rng) < ms.metallic)
+            {
+                float f = ref_pow5(1.f - local_cos_i);
+                fresnel_color = mk(ms.base_color.x + (1.f - ms.base_color.x) * f,
+                                   ms.base_color.y + (1.f - ms.base_color.y) * f,
+                                   ms.base_color.z + (1.f - ms.base_color.z) * f);
+                valid = true;
+            }
+            else
+            {
+                float fresnel = schlick1(local_cos_i, 0.04f);
+                if (rng_unit(rng) < fresnel)
+                {
+                    fresnel_color = mk(1.f, 1.f, 1.f);
+                    valid = true;
+                }
+            }
+        }
+        if (valid)
+        {
+            float occlusion = smith_ggx_correlated(cos_o, cos_in, ms.roughness);
+            float normalizer = geometry_schlick_ggx(cos_o, ms.roughness) + kEps;
+            throughput = mk(fresnel_color.x * occlusion / normalizer, fresnel_color.y * occlusion / normalizer,
+                            fresnel_color.z * occlusion / normalizer);
+            lwi = swi;
+        }
+        else
+        {
+            // LambertianBxDF::Sample -> CosineWeightedHemiSphere::Sample
+            float dx, dy;
+            unit_disk(rng, dx, dy);
+            float z = sqrtf(fmaxf(0.f, 1.0f - (dx * dx + dy * dy)));
+            lwi = mk(dx, dy, z);
+            throughput = ms.base_color;
+        }
+    }
+    // TransformBasisToWorld(...).normalized()
+    wi_world = normalized(mk(au.x * lwi.x + av.x * lwi.y + aw.x * lwi.z, au.y * lwi.x + av.y * lwi.y + aw.y * lwi.z,
+                             au.z * lwi.x + av.z * lwi.y + aw.z * lwi.z));
+    return throughput;
+}
+
+// ---- SkyRenderProxy::Evaluate ----
+__device__ __forceinline__ V3 sky_evaluate(const DScene &sc, V3 d)
+{
+    if (sc.sky.has_map)
+    {
+        // Image2DCube::DirectionToTextureCoordinate (io/Image.cpp:298-345); FaceId order +X,-X,+Y,-Y,+Z,-Z
+        float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z), u, v;
+        int face;
+        if (ax >= ay && ax >= az)
+        {
+            if (d.x > 0.f) { face = 0; u = -d.z / d.x; v = -d.y / d.x; }
+            else { face = 1; u = d.z / -d.x; v = -d.y / -d.x; }
+        }
+        else if (ay >= ax && ay >= az)
+        {
+            if (d.y > 0.f) { face = 2; u = d.x / d.y; v = d.z / d.y; }
+            else { face = 3; u = d.x / -d.y; v = -d.z / -d.y; }
+        }
+        else
+        {
+            if (d.z > 0.f) { face = 4; u = d.x / d.z; v = -d.y / d.z; }
+            else { face = 5; u = -d.x / -d.z; v = -d.y / -d.z; }
+        }
+        u = (u + 1.f) * 0.5f;
+        v = (v + 1.f) * 0.5f;
+        return sample_texture(sc.sky.faces[face], u, v);
+    }
+    float t = 0.5f * d.z + 0.5f;
+    return mk(1.f + (sc.sky.color[0] - 1.f) * t, 1.f + (sc.sky.color[1] - 1.f) * t, 1.f + (sc.sky.color[2] - 1.f) * t);
+}
+} // namespace spk
