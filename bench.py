@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the `cuda` path-tracing pipeline (contract: task statement; metric: BASELINE.json).
+
+Workload (configs[1], "C2"): TestScene-procedural on the cuda pipeline, 1920x1080, 256 spp, max depth 8, same seeds as
+the reference CPU path tracer. One STEP = one full render of that image (W*H*spp paths).
+  value   Mpaths/s, device-resident: scene, camera and accumulator already in HBM; CUDA events around the K steps.
+  e2e     the same metric through the C ABI with HOST buffers: per step the scene tables are uploaded from host memory
+          (spk_cuda_upload_scene), the image is rendered, tone-mapped and read back (spk_cuda_resolve) inside the timing.
+  N > 1   one process per GPU (torchrun); the spp range is interleaved over ranks (first_sample = rank, stride = N), the
+          accumulators are summed on rank 0 with ONE NCCL reduce, rank 0 resolves. Total work fixed -> "strong".
+  roofline   render kernel, HBM bound: algorithmic bytes (SURVEY.md 8d / DESIGN.md) from the kernel's own counters.
+  cpu_baseline / --impl reference: the reference's CPU path tracer (oracle/_ref, else the oracle port) on the host cores,
+          bounded sample of the same workload. oracle/ is loaded ONLY on those two legs.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WIDTH, HEIGHT, SPP, BOUNCE = 1920, 1080, 256, 8
+WORKLOAD = "TestScene-procedural, cuda pipeline, 1920x1080, 256 spp, max depth 8 (BASELINE.json configs[1])"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        busy = [x for x in sm if x > 0.5 * max(mx or [1])] or sm
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def scene_host_bytes(sb):
+    n = 0
+    for m in sb.meshes:
+        n += m.vertices.nbytes + m.normals.nbytes + m.tangents.nbytes + m.indices.nbytes + (m.uvs.nbytes if m.uvs is not None else 0)
+    for b in sb.blas:
+        n += b.nodes.nbytes + b.prim_ids.nbytes
+    if sb.tlas is not None:
+        n += sb.tlas.nodes.nbytes + sb.tlas.prim_ids.nbytes
+    n += sum(px.nbytes for px, _ in sb.textures)
+    n += 112 * len(sb.prims) + 64 * len(sb.materials)
+    return int(n)
+
+
+def load_oracle():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    for kind in ("reference", "port"):
+        if O.available(kind):
+            return O.Oracle(kind)
+    raise RuntimeError("no oracle library: make -C oracle")
+
+
+def cpu_render_rate(desc, cam, spp, first_sample=0):
+    """reference CPU path tracer on the host cores; returns (Mpaths/s, seconds, cores, kind)"""
+    orc = load_oracle()
+    cores = os.cpu_count() or 1
+    workers = max(1, min(64, cores) - 1)  # min(thread cvar 64, hw) - 1 reserved main thread (TaskDispatcher.cpp:19-24)
+    t0 = time.perf_counter()
+    orc.render(desc, cam, WIDTH, HEIGHT, first_sample, spp, max_bounce=BOUNCE, threads=workers)
+    dt = time.perf_counter() - t0
+    return WIDTH * HEIGHT * spp / dt / 1e6, dt, workers, orc.kind
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU path tracer, bounded sample per step (rank 0 only under torchrun)"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from sparkle_b200 import scenes
+    from sparkle_b200.scene import orbit_camera
+    sb, camkw = scenes.testscene()
+    desc = sb.finalize()
+    cam = orbit_camera(WIDTH, HEIGHT, **camkw)
+    spp_step = 1
+    for w in range(args.warmup):
+        cpu_render_rate(desc, cam, spp_step, first_sample=w)
+    t0 = time.perf_counter()
+    cores = kind = None
+    for s in range(args.steps):
+        _, _, cores, kind = cpu_render_rate(desc, cam, spp_step, first_sample=args.warmup + s)
+    dt = time.perf_counter() - t0
+    paths = WIDTH * HEIGHT * spp_step * args.steps
+    value = paths / dt / 1e6
+    sample = f"{spp_step} spp of {SPP} per step at {WIDTH}x{HEIGHT} ({args.steps} steps), extrapolates linearly in spp"
+    line = {"impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": cores,
+                             "kind": "reference" if kind == "reference" else "port", "sample": sample},
+            "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+class AccumView:
+    """torch view of the context's device accumulator (for the NCCL reduce), via __cuda_array_interface__"""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<f4", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+    from sparkle_b200 import _abi as A
+    from sparkle_b200 import scenes
+    from sparkle_b200.device import CudaContext
+    from sparkle_b200.scene import orbit_camera
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the cuda pipeline has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    assert SPP % world == 0, "spp must divide over the ranks"
+    spp_rank = SPP // world
+
+    sb, camkw = scenes.testscene()
+    desc = sb.finalize()
+    cam = orbit_camera(WIDTH, HEIGHT, **camkw)
+    ctx = CudaContext(WIDTH, HEIGHT, device=local)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)  # torch.cuda.Event sees this stream
+    ctx.upload_scene(desc)
+    ctx.set_camera(cam)
+    ptr, nbytes = ctx.accum_ptr()
+    accum_t = torch.as_tensor(AccumView(ptr, nbytes), device=f"cuda:{local}")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        ctx.reset_accumulation()
+        ctx.render(first_sample=rank, sample_count=spp_rank, sample_stride=world, max_bounce=BOUNCE)
+        if world > 1:
+            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+
+    def timed(step_fn, steps, warmup):
+        for _ in range(warmup):
+            flush.fill_(1)
+            step_fn()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for k in range(steps):
+            flush.fill_(k)  # L2 flush between timed iterations, outside the events
+            ev[k][0].record()
+            step_fn()
+            ev[k][1].record()
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- kernel counters (one untimed instrumented pass on a 1/16-spp sample) ----
+    ctx.reset_stats()
+    ctx.reset_accumulation()
+    cspp = max(1, spp_rank // 16)
+    ctx.render(first_sample=rank, sample_count=cspp, sample_stride=world, max_bounce=BOUNCE, flags=A.FLAG_COUNTERS)
+    cst = ctx.stats()
+    ctx.reset_stats()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.stats()["kernel_launches"]
+    ms_total = timed(device_step, args.steps, args.warmup)
+    launches = ctx.stats()["kernel_launches"] - launches0 - args.warmup
+    st = ctx.stats()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- e2e: host scene tables in, tone-mapped image out, every step ----
+    h2d = scene_host_bytes(sb)
+    d2h = WIDTH * HEIGHT * 8
+
+    def e2e_step():
+        ctx.upload_scene(desc)
+        ctx.set_camera(cam)
+        ctx.reset_accumulation()
+        ctx.render(first_sample=rank, sample_count=spp_rank, sample_stride=world, max_bounce=BOUNCE)
+        if world > 1:
+            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            ctx.resolve(A.RESOLVE_TONEMAP_F16, total_samples=SPP)
+
+    e2e_steps = max(1, min(args.steps, 3))
+    ms_e2e = timed(e2e_step, e2e_steps, 1)
+
+    paths_step = WIDTH * HEIGHT * SPP
+    value = paths_step * args.steps / (ms_total * 1e-3) / 1e6
+    e2e_value = paths_step * e2e_steps / (ms_e2e * 1e-3) / 1e6
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the render kernel (this rank's launch) ----
+    peak, peak_src = peaks()
+    scale = spp_rank / cspp
+    rays_launch = cst["rays"] * scale
+    paths_launch = WIDTH * HEIGHT * spp_rank
+    alg_bytes = (64 * cst["node_visits"] + 48 * cst["tri_tests"] + 128 * cst["inst_visits"] + 16 * cst["sphere_tests"]) * scale \
+        + 2 * 16 * WIDTH * HEIGHT
+    kernel_ms = ms_total / args.steps  # the render kernel is the step at N=1 (memset + 1 launch)
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    rays_total = st["rays"] / max(1, args.steps + args.warmup) * world
+    line = {
+        "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "parallelism": f"spp-split x{world}", "l2": "flushed between steps (256 MB fill)",
+                   "mrays_per_s": rays_total / (kernel_ms * 1e-3) / 1e6, "rays_per_path": rays_launch / paths_launch},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / e2e_steps},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "kernel": "render_kernel<CULL=true>",
+                     "alg_bytes_per_ray": alg_bytes / max(1.0, rays_launch),
+                     "node_visits_per_ray": cst["node_visits"] / max(1, cst["rays"]),
+                     "tri_tests_per_ray": cst["tri_tests"] / max(1, cst["rays"])},
+    }
+    if not args.no_cpu_baseline and world == 1:
+        v, dt, cores, kind = cpu_render_rate(desc, cam, 2)
+        line["cpu_baseline"] = {"value": v, "unit": "Mpaths/s", "cores": cores,
+                                "kind": "reference" if kind == "reference" else "port",
+                                "sample": f"2 spp of {SPP} at {WIDTH}x{HEIGHT} ({dt:.1f} s), linear in spp"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

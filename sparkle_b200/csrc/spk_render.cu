@@ -35,7 +35,7 @@ struct RenderArgs
     uint32_t cumulated; // samples already in the accumulator (running-average mode)
 };
 
-template <bool CULL>
+template <bool CULL, bool COUNT>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
     render_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
                   unsigned long long *__restrict__ counters)
@@ -46,6 +46,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
     const uint32_t i = (warp % tiles_x) * kTileW + (lane & (kTileW - 1));
     const uint32_t j = (warp / tiles_x) * kTileH + (lane / kTileW);
     uint32_t rays = 0;
+    TraceCounters cnt{0, 0, 0, 0};
     if (i < a.width && j < a.height)
     {
         const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
@@ -57,7 +58,6 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
         const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
         float4 acc = accum[size_t(j) * a.width + i];
         uint32_t stack[64];
-        TraceCounters cnt{0, 0, 0, 0};
         for (uint32_t s = 0; s < a.sample_count; s++)
         {
             // CPURenderer.cpp:442-443, unsigned wrap
@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
             for (uint32_t bounce = 0; bounce < a.max_bounce; bounce++)
             {
                 Hit hit;
-                trace_closest<CULL, false>(sc, origin, dir, hit, stack, cnt);
+                trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
                 rays++;
                 if (hit.inst == SPK_INVALID_ID)
                 {
@@ -145,6 +145,19 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
     {
         atomicAdd(counters + 0, (unsigned long long)pixels * a.sample_count);
         atomicAdd(counters + 1, (unsigned long long)total);
+    }
+    if (COUNT)
+    {
+        uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+        {
+            uint32_t sum = __reduce_add_sync(0xffffffffu, v[k]);
+            if (lane == 0 && sum)
+            {
+                atomicAdd(counters + 2 + k, (unsigned long long)sum);
+            }
+        }
     }
 }
 
@@ -213,10 +226,18 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
     uint32_t tiles = ((a.width + kTileW - 1) / kTileW) * ((a.height + kTileH - 1) / kTileH);
     dim3 grid{(tiles + kWarpsPerBlock - 1) / kWarpsPerBlock}, block{kWarpsPerBlock * 32};
     const DScene &scene = ctx->scene;
-    if (p->flags & SPK_FLAG_EXACT_TRAVERSAL)
-        render_kernel<false><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters);
+    const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
+#define SPK_LAUNCH_RENDER(C, N)                                                                                        \
+    render_kernel<C, N><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters)
+    if (exact && count)
+        SPK_LAUNCH_RENDER(false, true);
+    else if (exact)
+        SPK_LAUNCH_RENDER(false, false);
+    else if (count)
+        SPK_LAUNCH_RENDER(true, true);
     else
-        render_kernel<true><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters);
+        SPK_LAUNCH_RENDER(true, false);
+#undef SPK_LAUNCH_RENDER
     SPK_CUDA_TRY(cudaGetLastError());
     ctx->stats.kernel_launches++;
     return SPK_OK;
