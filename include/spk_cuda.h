@@ -171,7 +171,9 @@ typedef enum SpkAccumMode {
 enum {
     SPK_FLAG_EXACT_TRAVERSAL = 1u, /* never shorten tmax while traversing (reference behaviour) */
     SPK_FLAG_COUNTERS = 2u,        /* instrumented kernel: fill node/triangle counters in SpkStats */
-    SPK_FLAG_WAVEFRONT = 4u        /* wavefront (queue) tracer instead of the persistent megakernel */
+    SPK_FLAG_WAVEFRONT = 4u,       /* wavefront (queue) tracer instead of the persistent megakernel */
+    SPK_FLAG_THREAD_PER_RAY = 8u   /* ray batches: plain one-thread-per-ray kernel instead of the persistent warp-voting one
+                                      (kept for A/B measurement; same results) */
 };
 
 typedef struct SpkRenderParams {

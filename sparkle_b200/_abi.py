@@ -14,7 +14,7 @@ PRIM_MESH, PRIM_SPHERE = 0, 1
 MAT_PBR, MAT_DIELECTRIC = 0, 1
 FMT_RGBA8_UNORM, FMT_RGBA8_SRGB, FMT_RGBA16F, FMT_RGBA32F = 0, 1, 2, 3
 ACCUM_SUM, ACCUM_RUNNING_AVERAGE = 0, 1
-FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT = 1, 2, 4
+FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY = 1, 2, 4, 8
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
 
 u32, i32, f32, u64 = C.c_uint32, C.c_int32, C.c_float, C.c_uint64

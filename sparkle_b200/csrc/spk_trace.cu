@@ -8,7 +8,10 @@
  * (SURVEY.md 8d), with the N counted by the COUNT=true instantiation of the same code.
  */
 #include "spk_context.h"
+
+#include <cstdlib>
 #include "spk_traverse.cuh"
+#include "spk_traverse_warp.cuh"
 
 namespace spk
 {
@@ -52,7 +55,148 @@ __global__ void __launch_bounds__(kTraceThreads)
         }
     }
 }
+
+// ---- persistent, warp-converged form (spk_traverse_warp.cuh): the default for ray batches ----
+constexpr int kPersistWarps = 4;
+
+template <bool CULL, bool COUNT, int LEAF_VOTE>
+__global__ void __launch_bounds__(kPersistWarps * 32)
+    trace_persistent_kernel(const DScene sc, const float4 *__restrict__ rays, unsigned long long n,
+                            float *__restrict__ hits, unsigned long long *__restrict__ counters,
+                            unsigned long long *__restrict__ next_ray)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    uint32_t stack[kWarpStack];
+    LaneState s;
+    TraceCounters cnt{0, 0, 0, 0};
+    unsigned long long ray_id = ~0ull;
+    bool active = false;
+    bool exhausted = false; // warp-uniform: the global counter has passed n
+    const float4 *__restrict__ pairs = sc.pairs;
+    for (;;)
+    {
+        // ---- refill idle lanes from the global ray counter
+        unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && exhausted)
+        {
+            if (idle == 0xffffffffu)
+            {
+                break;
+            }
+        }
+        else if (idle)
+        {
+            unsigned long long base = 0;
+            int leader = __ffs(idle) - 1;
+            if ((int)lane == leader)
+            {
+                base = atomicAdd(next_ray, (unsigned long long)__popc(idle));
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active)
+            {
+                unsigned long long id = base + __popc(idle & lt_mask);
+                if (id < n && sc.num_instances != 0)
+                {
+                    float4 ro = __ldg(rays + 2 * id), rd = __ldg(rays + 2 * id + 1);
+                    lane_begin<CULL>(sc, s, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z));
+                    ray_id = id;
+                    active = true;
+                }
+                else if (id < n)
+                {
+                    float *o = hits + 5 * id; // empty scene: every ray misses
+                    o[0] = SPK_FLT_MAX;
+                    o[1] = 0.f;
+                    o[2] = 0.f;
+                    o[3] = __uint_as_float(SPK_INVALID_ID);
+                    o[4] = __uint_as_float(SPK_INVALID_ID);
+                }
+            }
+            exhausted = base + __popc(idle) >= n;
+            if (base >= n && !__any_sync(0xffffffffu, active))
+            {
+                break;
+            }
+        }
+        // ---- inner phase
+        for (;;)
+        {
+            bool inner = active && (s.top & 15u) == 0u;
+            unsigned m_inner = __ballot_sync(0xffffffffu, inner);
+            unsigned m_leaf = __ballot_sync(0xffffffffu, active && !inner);
+            if (m_inner == 0u || __popc(m_leaf) >= LEAF_VOTE)
+            {
+                break;
+            }
+            if (inner)
+            {
+                active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
+            }
+        }
+        // ---- leaf phase (one item per lane); finished lanes write their hit
+        if (active && (s.top & 15u) != 0u)
+        {
+            active = lane_leaf_step<CULL, COUNT>(sc, s, stack, cnt);
+        }
+        // lanes that ran out of stack in either phase
+        if (!active && ray_id != ~0ull)
+        {
+            float *o = hits + 5 * ray_id;
+            o[0] = s.best.t;
+            o[1] = s.best.u;
+            o[2] = s.best.v;
+            uint32_t prim = s.best.inst == SPK_INVALID_ID ? SPK_INVALID_ID : __ldg(&sc.instances[s.best.inst].prim);
+            o[3] = __uint_as_float(prim);
+            o[4] = __uint_as_float(s.best.face);
+            ray_id = ~0ull;
+        }
+    }
+    if (COUNT)
+    {
+        uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+        {
+            uint32_t sum = __reduce_add_sync(0xffffffffu, v[k]);
+            if (lane == 0 && sum)
+            {
+                atomicAdd(counters + 2 + k, (unsigned long long)sum);
+            }
+        }
+    }
+}
 } // namespace
+
+static int leaf_vote_setting()
+{
+    static int v = [] {
+        const char *e = getenv("SPK_LEAF_VOTE");
+        return e ? atoi(e) : 16;
+    }();
+    return v;
+}
+
+template <bool CULL, bool COUNT, int VOTE>
+static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, float *hits)
+{
+    auto kernel = trace_persistent_kernel<CULL, COUNT, VOTE>;
+    static int blocks_per_sm = 0, sms = 0;
+    if (blocks_per_sm == 0)
+    {
+        SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, 0));
+        SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+        blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
+    }
+    uint64_t want = (n + kPersistWarps * 32 - 1) / (kPersistWarps * 32);
+    uint64_t resident = uint64_t(blocks_per_sm) * sms; // one wave of persistent CTAs: a multiple of the SM count
+    unsigned grid = unsigned(want < resident ? want : resident);
+    unsigned long long *next_ray = ctx->d_counters + 7;
+    SPK_CUDA_TRY(cudaMemsetAsync(next_ray, 0, sizeof(unsigned long long), ctx->stream));
+    kernel<<<grid, kPersistWarps * 32, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters, next_ray);
+    return SPK_OK;
+}
 
 int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags)
 {
@@ -60,24 +204,51 @@ int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *
     {
         return SPK_OK;
     }
-    uint64_t blocks = (n + kTraceThreads - 1) / kTraceThreads;
-    if (blocks > 0x7fffffffull)
-    {
-        set_error("spk_cuda_trace_closest: batch too large for one launch");
-        return SPK_ERR_INVALID_ARGUMENT;
-    }
     bool exact = flags & SPK_FLAG_EXACT_TRAVERSAL, count = flags & SPK_FLAG_COUNTERS;
     auto *rays = static_cast<const float4 *>(d_rays);
     auto *hits = static_cast<float *>(d_hits);
-    dim3 grid{unsigned(blocks)}, block{kTraceThreads};
-    if (exact && count)
-        trace_closest_kernel<false, true><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    int rc = SPK_OK;
+    if (flags & SPK_FLAG_THREAD_PER_RAY)
+    {
+        uint64_t blocks = (n + kTraceThreads - 1) / kTraceThreads;
+        if (blocks > 0x7fffffffull)
+        {
+            set_error("spk_cuda_trace_closest: batch too large for one thread-per-ray launch");
+            return SPK_ERR_INVALID_ARGUMENT;
+        }
+        dim3 grid{unsigned(blocks)}, block{kTraceThreads};
+        if (exact && count)
+            trace_closest_kernel<false, true><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+        else if (exact)
+            trace_closest_kernel<false, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+        else if (count)
+            trace_closest_kernel<true, true><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+        else
+            trace_closest_kernel<true, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    }
+    else if (exact && count)
+        rc = launch_persistent<false, true, 16>(ctx, rays, n, hits);
     else if (exact)
-        trace_closest_kernel<false, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+        rc = launch_persistent<false, false, 16>(ctx, rays, n, hits);
     else if (count)
-        trace_closest_kernel<true, true><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+        rc = launch_persistent<true, true, 16>(ctx, rays, n, hits);
     else
-        trace_closest_kernel<true, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
+    {
+        switch (leaf_vote_setting())
+        {
+        case 1: rc = launch_persistent<true, false, 1>(ctx, rays, n, hits); break;
+        case 4: rc = launch_persistent<true, false, 4>(ctx, rays, n, hits); break;
+        case 8: rc = launch_persistent<true, false, 8>(ctx, rays, n, hits); break;
+        case 12: rc = launch_persistent<true, false, 12>(ctx, rays, n, hits); break;
+        case 24: rc = launch_persistent<true, false, 24>(ctx, rays, n, hits); break;
+        case 32: rc = launch_persistent<true, false, 32>(ctx, rays, n, hits); break;
+        default: rc = launch_persistent<true, false, 16>(ctx, rays, n, hits); break;
+        }
+    }
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
     SPK_CUDA_TRY(cudaGetLastError());
     ctx->stats.kernel_launches++;
     ctx->stats.rays += n;

@@ -95,8 +95,9 @@ __device__ __forceinline__ void intersect_triangle(const float4 *__restrict__ tr
     if (t > 1e-6f)
     {
         V3 lp = o + d * t;                    // Ray::At
-        V3 wp = xform_point(fwd, lp);         // Transform::TransformPoint
-        float world_t = (wp.x - wo.x) / wd.x; // Ray::InverseAt: x component only
+        // Transform::TransformPoint, then Ray::InverseAt which reads the x component only: row 0 suffices
+        float wpx = ((fwd[0] * lp.x + fwd[1] * lp.y) + fwd[2] * lp.z) + fwd[3];
+        float world_t = (wpx - wo.x) / wd.x;
         if (world_t > 0.f && world_t < best.t)
         {
             best.t = world_t;

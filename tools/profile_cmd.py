@@ -31,7 +31,7 @@ if what in ("both", "trace"):
     hits = torch.empty((n_rays, 5), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
     for k in range(2):
-        ctx.trace_closest_device(rays.data_ptr(), n_rays, hits.data_ptr(), 0)
+        ctx.trace_closest_device(rays.data_ptr(), n_rays, hits.data_ptr(), A.FLAG_THREAD_PER_RAY if os.environ.get('SPK_TPR') else 0)
         ctx.synchronize()
         ms = ctx.stats()["last_ms"]
         print("trace", n_rays, "rays ms", ms, "Mrays/s", n_rays / ms / 1e3)
