@@ -100,3 +100,57 @@ class Oracle:
         if rc != 0:
             raise RuntimeError(f"orc_resolve -> {rc}")
         return out
+
+    # ---- known-answer probes (oracle.h orc_kat_*) ----
+    def rng_state(self, seed):
+        out = np.zeros(4, np.uint32)
+        self.lib.orc_rng_state(seed, out.ctypes.data_as(A.u32p))
+        return out
+
+    def rng_units(self, seed, n):
+        out = np.zeros(n, np.float32)
+        self.lib.orc_rng_units(seed, n, out.ctypes.data_as(A.fp))
+        return out
+
+    def kat_vec(self, op, a, b=None, m=None):
+        a = np.ascontiguousarray(a, np.float32)
+        b = np.ascontiguousarray(b if b is not None else np.zeros(3), np.float32)
+        m = np.ascontiguousarray(m if m is not None else np.eye(4)[:3], np.float32).reshape(12)
+        out = np.zeros(3, np.float32)
+        self.lib.orc_kat_vec(op, a.ctypes.data_as(A.fp), b.ctypes.data_as(A.fp), m.ctypes.data_as(A.fp),
+                             out.ctypes.data_as(A.fp))
+        return out
+
+    def kat_libm(self, op, x, y=0.0):
+        return np.float32(self.lib.orc_kat_libm(op, float(x), float(y)))
+
+    def unit_disk(self, seed):
+        out = np.zeros(2, np.float32)
+        self.lib.orc_kat_unit_disk(seed, out.ctypes.data_as(A.fp))
+        return out
+
+    def texture(self, pixels, fmt, u, v):
+        px = np.ascontiguousarray(pixels)
+        t = A.TextureDesc(px.ctypes.data, px.shape[1], px.shape[0], fmt, 0)
+        out = np.zeros(3, np.float32)
+        self.lib.orc_kat_texture(C.byref(t), float(u), float(v), out.ctypes.data_as(A.fp))
+        return out
+
+    def sky(self, sky_desc, direction):
+        d = np.ascontiguousarray(direction, np.float32)
+        out = np.zeros(3, np.float32)
+        self.lib.orc_kat_sky(C.byref(sky_desc), d.ctypes.data_as(A.fp), out.ctypes.data_as(A.fp))
+        return out
+
+    def sample_surface(self, desc, material, seed, direction, normal, tangent, uv):
+        arrs = [np.ascontiguousarray(x, np.float32) for x in (direction, normal, tangent, uv)]
+        wi, thr = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        draws = self.lib.orc_kat_sample_surface(C.byref(desc), material, seed, *[a.ctypes.data_as(A.fp) for a in arrs],
+                                                wi.ctypes.data_as(A.fp), thr.ctypes.data_as(A.fp))
+        return wi, thr, draws
+
+    def intersect_full(self, desc, ray):
+        r = np.ascontiguousarray(ray, np.float32).reshape(8)
+        out = np.zeros(12, np.float32)
+        prim = self.lib.orc_intersect_full(C.byref(desc), r.ctypes.data, out.ctypes.data_as(A.fp))
+        return prim, out

@@ -1,0 +1,163 @@
+"""CPU tests of the oracle (no GPU): the C++ port (oracle/liboracle.so) against
+  - tests/golden/reference_vectors.npz, generated from the reference's OWN CPU path tracer (oracle/_ref, the reference
+    translation units compiled in place) by tests/golden/make_golden.py  -> bit for bit;
+  - the reference library itself where it is built (this container)         -> bit for bit, larger cases;
+  - known answers probed from the vendored XoshiroCpp.hpp;
+  - brute force (every primitive, every triangle), which is BVH-topology independent.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import golden_cases as G
+import oracle_lib as O
+from sparkle_b200 import _abi as A
+from sparkle_b200 import geometry, scenes
+from sparkle_b200.scene import orbit_camera
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.npz")
+
+
+def bits(x):
+    x = np.ascontiguousarray(x)
+    return x.view(np.uint32) if x.dtype == np.float32 else x
+
+
+def assert_same_bits(got, want, what):
+    assert got.shape == want.shape and got.dtype == want.dtype, f"{what}: {got.shape}/{got.dtype} vs {want.shape}/{want.dtype}"
+    bad = np.nonzero(bits(got).reshape(-1) != bits(want).reshape(-1))[0]
+    assert bad.size == 0, f"{what}: {bad.size} of {got.size} elements differ; first at {bad[:5]}: " \
+                          f"{got.reshape(-1)[bad[:5]]} vs {want.reshape(-1)[bad[:5]]}"
+
+
+@pytest.fixture(scope="module")
+def port():
+    if not O.available("port"):
+        pytest.fail("oracle/liboracle.so missing: make -C oracle")
+    o = O.Oracle("port")
+    assert o.kind == "port"
+    return o
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return dict(np.load(GOLDEN))
+
+
+def test_port_matches_reference_golden_vectors(port, golden):
+    got = G.evaluate(port)
+    assert sorted(got) == sorted(golden)
+    for k in sorted(golden):
+        assert_same_bits(got[k], golden[k], f"golden[{k}]")
+
+
+@pytest.mark.skipif(not O.available("reference"), reason="oracle/_ref not built (needs /root/reference)")
+def test_reference_reproduces_golden_vectors(golden):
+    ref = O.Oracle("reference")
+    assert ref.kind == "reference"
+    got = G.evaluate(ref)
+    for k in sorted(golden):
+        assert_same_bits(got[k], golden[k], f"golden[{k}]")
+
+
+def test_rng_known_answers(port):
+    # SURVEY.md 8a row a1, probed from thirdparty/xoshiro_cpp/XoshiroCpp.hpp
+    assert [f"{x:08x}" for x in port.rng_state(0)] == ["7b1dcdaf", "a1b965f4", "8009454f", "724c81ec"]
+    u = port.rng_units(12345, 2)
+    assert float(u[0]).hex() == "0x1.84151a0000000p-6" and float(u[1]).hex() == "0x1.a33ba40000000p-2"
+    # the python generator that seeds the procedural scenes is the same stream
+    for seed in G.RNG_SEEDS:
+        g = geometry.Xoshiro128Plus(seed)
+        mine = np.array([g.unit() for _ in range(16)], np.float32)
+        assert_same_bits(mine, port.rng_units(seed, 16), f"python xoshiro seed {seed}")
+
+
+def test_eigen_association(port):
+    """H4: the association the reference's Eigen expressions compile to; a case where the other order differs"""
+    a, b = np.array([1e8, 1.0, -1e8], np.float32), np.array([1.0, 1.0, 1.0], np.float32)
+    assert port.kat_vec(0, a, b)[0] == np.float32(np.float32(np.float32(1e8) + np.float32(1.0)) + np.float32(-1e8))
+    a = np.array([1.0, 3e-4, 3e-4], np.float32)
+    want = np.float32(a[0] * a[0]) + np.float32(np.float32(a[1] * a[1]) + np.float32(a[2] * a[2]))
+    assert port.kat_vec(1, a)[0] == np.float32(want)
+
+
+@pytest.mark.parametrize("name", G.SCENES)
+def test_bvh_traversal_equals_brute_force(port, name):
+    """closest hit is topology independent except for exact-t ties (strict <): BVH, culled BVH and brute force agree"""
+    sb, _, rays, _ = G.small_scene(name)
+    desc = sb.finalize()
+    bvh, c0 = port.trace_closest(desc, rays)
+    brute, c1 = port.trace_closest(desc, rays, mode=O.TRACE_BRUTE_FORCE)
+    culled, c2 = port.trace_closest(desc, rays, mode=O.TRACE_BVH_CULLED)
+    assert_same_bits(bvh["t"], brute["t"], f"{name} t bvh vs brute")
+    assert_same_bits(bvh["t"], culled["t"], f"{name} t bvh vs culled")
+    tie_free = bvh["prim"] == brute["prim"]
+    assert tie_free.mean() > 0.999
+    assert np.array_equal(bvh["prim"], culled["prim"]) and np.array_equal(bvh["face"], culled["face"])
+    assert c2.node_visits <= c0.node_visits and c0.tri_tests <= c1.tri_tests
+    assert (bvh["prim"] != A.INVALID_ID).mean() > 0.05
+
+
+def test_empty_and_degenerate(port):
+    sb = scenes.SceneBuilder()
+    sb.set_sky((0.5, 0.7, 1.0))
+    desc = sb.finalize()
+    rays = geometry.random_rays(8, seed=1)
+    hits, _ = port.trace_closest(desc, rays, threads=1)
+    assert (hits["prim"] == A.INVALID_ID).all() and (hits["t"] == np.finfo(np.float32).max).all()
+    # zero rays
+    hits, _ = port.trace_closest(desc, np.zeros((0, 8), np.float32))
+    assert len(hits) == 0
+    # d.x == 0 drops every mesh hit (world_t = (p.x - o.x) / d.x is NaN/inf); spheres are unaffected
+    sb, _ = scenes.testscene()
+    desc = sb.finalize()
+    r = np.zeros((2, 8), np.float32)
+    r[0, 0:3], r[0, 4:7] = (5, 4, 10), (0, 0, -1)   # over the box stand-in: mesh + floor, both dropped
+    r[1, 0:3], r[1, 4:7] = (0, 0, 10), (0, 0, -1)   # over the glass sphere
+    hits, _ = port.trace_closest(desc, r, threads=1)
+    assert hits["prim"][0] == A.INVALID_ID and hits["prim"][1] == 1 and hits["t"][1] == np.float32(6.0)
+
+
+def test_sample_split_invariance(port):
+    """sample s of pixel p depends only on (p, s): any split of the sample range gives the same set of samples"""
+    sb, camkw, _, bounce = G.small_scene("testscene")
+    desc = sb.finalize()
+    w, h = 40, 24
+    cam = orbit_camera(w, h, **camkw)
+    whole, _ = port.render(desc, cam, w, h, 0, 4, max_bounce=bounce)
+    a, _ = port.render(desc, cam, w, h, 0, 2, max_bounce=bounce, sample_stride=2)
+    b, _ = port.render(desc, cam, w, h, 1, 2, max_bounce=bounce, sample_stride=2)
+    assert np.allclose(a + b, whole, rtol=1e-6, atol=1e-6)
+    one, _ = port.render(desc, cam, w, h, 2, 1, max_bounce=bounce)
+    px = port.sample_pixel(desc, cam, w, h, 7, 5, 2, max_bounce=bounce)
+    assert_same_bits(px[:4], one[5, 7], "sample_pixel vs render")
+
+
+@pytest.mark.skipif(not O.available("reference"), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("name,n_rays,spp", [("testscene", 60000, 4), ("room", 30000, 2), ("city", 30000, 2)])
+def test_port_equals_reference_larger(port, name, n_rays, spp):
+    ref = O.Oracle("reference")
+    if name == "testscene":
+        sb, camkw = scenes.testscene()
+        rays = geometry.random_rays(n_rays, seed=13, extent=14.0)
+        bounce = 8
+    elif name == "room":
+        sb, camkw = scenes.room(num_objects=20, tex=32)
+        rays = geometry.random_rays(n_rays, seed=15, extent=4.5)
+        bounce = 32
+    else:
+        sb, camkw = scenes.city(num_meshes=4, tris_per_mesh=800, num_instances=24)
+        camkw = dict(camkw, radius=30.0)
+        rays = geometry.random_rays(n_rays, seed=14, extent=20.0)
+        bounce = 8
+    desc = sb.finalize()
+    hr, _ = ref.trace_closest(desc, rays)
+    hp, _ = port.trace_closest(desc, rays)
+    for f in ("prim", "face", "t", "u", "v"):
+        assert_same_bits(hp[f], hr[f], f"{name} hit.{f}")
+    w, h = 96, 64
+    cam = orbit_camera(w, h, **camkw)
+    ar, _ = ref.render(desc, cam, w, h, 5, spp, max_bounce=bounce)
+    ap, _ = port.render(desc, cam, w, h, 5, spp, max_bounce=bounce)
+    assert_same_bits(ap, ar, f"{name} accumulation image")
