@@ -58,129 +58,83 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
         const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
         float4 acc = accum[size_t(j) * a.width + i];
         uint32_t stack[64];
-        // Flat path loop: one iteration = one path segment (trace + shade). A lane whose path ended accumulates it and
-        // starts its pixel's next sample in the same loop, so lanes never wait at a per-sample reconvergence point for
-        // the longest path of the warp (1.9 segments per path on average, up to max_bounce). The samples of one pixel
-        // are still added in order s = 0, 1, 2, ... by the one thread that owns the pixel.
-        uint32_t s = 0, bounce = 0;
-        bool need_path = true;
-        Rng rng;
-        V3 origin, dir, throughput, color;
-        float valid = 1.f;
-        for (;;)
+        for (uint32_t s = 0; s < a.sample_count; s++)
         {
-            if (need_path)
+            // CPURenderer.cpp:442-443, unsigned wrap
+            const uint32_t frame_seed = a.first_sample + s * a.sample_stride;
+            Rng rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+            float u = ((float)i + rng_unit(rng)) * pw;
+            float v = ((float)j + rng_unit(rng)) * ph;
+            // SetupViewRay
+            float dx, dy;
+            unit_disk(rng, dx, dy);
+            dx = dx * cam.aperture_radius;
+            dy = dy * cam.aperture_radius;
+            V3 origin = cpos + (dx * cright + dy * cup);
+            V3 target = lower_left + u * max_u + v * max_v;
+            V3 dir = normalized(target - origin);
+
+            V3 throughput = mk(1.f, 1.f, 1.f), color = mk(0.f, 0.f, 0.f);
+            float valid = 1.f;
+            for (uint32_t bounce = 0; bounce < a.max_bounce; bounce++)
             {
-                if (s >= a.sample_count)
-                {
-                    break;
-                }
-                // CPURenderer.cpp:442-443, unsigned wrap
-                const uint32_t frame_seed = a.first_sample + s * a.sample_stride;
-                rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
-                float u = ((float)i + rng_unit(rng)) * pw;
-                float v = ((float)j + rng_unit(rng)) * ph;
-                // SetupViewRay
-                float dx, dy;
-                unit_disk(rng, dx, dy);
-                dx = dx * cam.aperture_radius;
-                dy = dy * cam.aperture_radius;
-                origin = cpos + (dx * cright + dy * cup);
-                V3 target = lower_left + u * max_u + v * max_v;
-                dir = normalized(target - origin);
-                throughput = mk(1.f, 1.f, 1.f);
-                color = mk(0.f, 0.f, 0.f);
-                valid = 1.f;
-                bounce = 0;
-                need_path = false;
-            }
-            bool done = false;
-            Hit hit;
-            hit.inst = SPK_INVALID_ID;
-            if (a.max_bounce != 0u)
-            {
+                Hit hit;
                 trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
                 rays++;
-            }
-            if (a.max_bounce == 0u)
-            {
-                done = true; // a zero-iteration bounce loop: the sample is black and valid
-            }
-            else if (hit.inst == SPK_INVALID_ID)
-            {
-                if (sc.sky.has_sky)
+                if (hit.inst == SPK_INVALID_ID)
                 {
-                    color = color + cmul(sky_evaluate(sc, dir), throughput);
+                    if (sc.sky.has_sky)
+                    {
+                        color = color + cmul(sky_evaluate(sc, dir), throughput);
+                    }
+                    break;
                 }
-                done = true;
-            }
-            else
-            {
                 Surface sf;
                 get_intersection(sc, origin, dir, hit, sf);
-                V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
                 if (a.debug)
                 {
                     // parity probes (tests only): first-hit normal / tangent / (u, v, t)
                     color = a.debug == 1 ? sf.normal : a.debug == 2 ? sf.tangent : mk(sf.u, sf.v, hit.t);
-                    done = true;
+                    break;
                 }
-                else if (norm(emissive) > kEps)
+                V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
+                if (norm(emissive) > kEps)
                 {
                     color = color + cmul(emissive, throughput);
-                    done = true;
+                    break;
                 }
-                else
+                V3 next_dir;
+                V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
+                throughput = cmul(throughput, this_throughput);
+                if (sqnorm(throughput) < kEps)
                 {
-                    V3 next_dir;
-                    V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
-                    throughput = cmul(throughput, this_throughput);
-                    if (sqnorm(throughput) < kEps)
-                    {
-                        valid = -1.f;
-                        done = true;
-                    }
-                    else
-                    {
-                        if (bounce >= 3)
-                        {
-                            float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
-                            p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
-                            if (rng_unit(rng) > p)
-                            {
-                                done = true;
-                            }
-                            else
-                            {
-                                throughput = throughput / p;
-                            }
-                        }
-                        if (!done)
-                        {
-                            origin = sf.location + next_dir * kTolerance;
-                            dir = next_dir;
-                            bounce++;
-                            done = bounce >= a.max_bounce; // the bounce cap adds nothing (CPURenderer.cpp:256)
-                        }
-                    }
+                    valid = -1.f;
+                    break;
                 }
+                if (bounce >= 3)
+                {
+                    float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
+                    p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
+                    if (rng_unit(rng) > p)
+                    {
+                        break;
+                    }
+                    throughput = throughput / p;
+                }
+                origin = sf.location + next_dir * kTolerance;
+                dir = next_dir;
             }
-            if (done)
+            color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
+            if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
             {
-                color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
-                if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
-                {
-                    uint32_t n = a.cumulated + s;
-                    float ma = (float)n / (float)(n + 1u);
-                    acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
-                                      lerp1(valid, acc.w, ma));
-                }
-                else
-                {
-                    acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
-                }
-                s++;
-                need_path = true;
+                uint32_t n = a.cumulated + s;
+                float ma = (float)n / (float)(n + 1u);
+                acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
+                                  lerp1(valid, acc.w, ma));
+            }
+            else
+            {
+                acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
             }
         }
         accum[size_t(j) * a.width + i] = acc;
