@@ -123,6 +123,19 @@ HOST_SYMBOLS = {
     "spk_host_bvh_nodes": (C.c_void_p, [C.c_void_p]),
     "spk_host_bvh_prim_ids": (C.c_void_p, [C.c_void_p]),
     "spk_host_bvh_sah_cost": (C.c_double, [C.c_void_p]),
+    # host/cuda_renderer.h: RenderConfig / CudaRenderer / headless frame loop
+    "spk_host_app_create": (C.c_void_p, [C.c_char_p, C.c_int]),
+    "spk_host_app_destroy": (None, [C.c_void_p]),
+    "spk_host_last_error": (C.c_char_p, []),
+    "spk_host_app_frame": (C.c_int, [C.c_void_p]),
+    "spk_host_app_run": (C.c_int, [C.c_void_p, u32]),
+    "spk_host_app_scene": (C.POINTER(SceneDesc), [C.c_void_p]),
+    "spk_host_app_camera": (C.POINTER(Camera), [C.c_void_p]),
+    "spk_host_app_cumulated_samples": (u32, [C.c_void_p]),
+    "spk_host_app_read_linear": (C.c_int, [C.c_void_p, fp, C.c_size_t]),
+    "spk_host_app_save_screenshot": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "spk_host_app_move_primitive": (C.c_int, [C.c_void_p, u32, f32, f32, f32]),
+    "spk_host_parse_pipeline": (C.c_int, [C.c_char_p]),
 }
 
 _libs = {}
