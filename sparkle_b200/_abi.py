@@ -148,7 +148,7 @@ def _load(name, symbols):
     if not os.path.exists(path):
         raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                            "(make -C sparkle_b200). The cuda pipeline has no fallback.")
-    lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
+    lib = C.CDLL(path)  # RTLD_LOCAL: the static cudart inside must not interpose on torch's
     for sym, (res, args) in symbols.items():
         fn = getattr(lib, sym)  # AttributeError if the library does not export what the header declares
         fn.restype = res

@@ -88,7 +88,7 @@ def test_create_renderer_has_no_fallback():
     with pytest.raises(RuntimeError, match="cuda"):
         app.HostApp("--pipeline forward --width 64 --height 48")
     with pytest.raises(RuntimeError):
-        app.HostApp("--pipeline cuda --width 64")          # odd token count
+        app.HostApp("--pipeline cuda --width")             # odd token count
     with pytest.raises(RuntimeError, match="unknown config"):
         app.HostApp("--pipeline cuda --no_such_cvar 1")
     with pytest.raises(RuntimeError, match="bad value"):
