@@ -120,13 +120,13 @@ def run_reference(args):
     sb, camkw = scenes.testscene()
     desc = sb.finalize()
     cam = orbit_camera(WIDTH, HEIGHT, **camkw)
-    spp_step = 1
+    spp_step = 16  # ~1.7 s of CPU work per step on 15 workers
     for w in range(args.warmup):
-        cpu_render_rate(desc, cam, spp_step, first_sample=w)
+        cpu_render_rate(desc, cam, spp_step, first_sample=w * spp_step)
     t0 = time.perf_counter()
     cores = kind = None
     for s in range(args.steps):
-        _, _, cores, kind = cpu_render_rate(desc, cam, spp_step, first_sample=args.warmup + s)
+        _, _, cores, kind = cpu_render_rate(desc, cam, spp_step, first_sample=(args.warmup + s) * spp_step)
     dt = time.perf_counter() - t0
     paths = WIDTH * HEIGHT * spp_step * args.steps
     value = paths / dt / 1e6
@@ -154,7 +154,7 @@ def run_cuda(args):
     import torch
     import torch.distributed as dist
     from sparkle_b200 import _abi as A
-    from sparkle_b200 import scenes
+    from sparkle_b200 import multi_gpu, scenes
     from sparkle_b200.device import CudaContext
     from sparkle_b200.scene import orbit_camera
 
@@ -166,8 +166,7 @@ def run_cuda(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    assert SPP % world == 0, "spp must divide over the ranks"
-    spp_rank = SPP // world
+    first_sample, spp_rank, stride = multi_gpu.sample_slice(SPP, rank, world)
 
     sb, camkw = scenes.testscene()
     desc = sb.finalize()
@@ -188,9 +187,8 @@ def run_cuda(args):
 
     def device_step():
         ctx.reset_accumulation()
-        ctx.render(first_sample=rank, sample_count=spp_rank, sample_stride=world, max_bounce=BOUNCE)
-        if world > 1:
-            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+        ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE)
+        multi_gpu.reduce_accumulator(accum_t, world, dst=0)  # ONE NCCL reduce over NVLink
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):
@@ -214,7 +212,7 @@ def run_cuda(args):
     ctx.reset_stats()
     ctx.reset_accumulation()
     cspp = max(1, spp_rank // 16)
-    ctx.render(first_sample=rank, sample_count=cspp, sample_stride=world, max_bounce=BOUNCE, flags=A.FLAG_COUNTERS)
+    ctx.render(first_sample=first_sample, sample_count=cspp, sample_stride=stride, max_bounce=BOUNCE, flags=A.FLAG_COUNTERS)
     cst = ctx.stats()
     ctx.reset_stats()
 
@@ -235,9 +233,8 @@ def run_cuda(args):
         ctx.upload_scene(desc)
         ctx.set_camera(cam)
         ctx.reset_accumulation()
-        ctx.render(first_sample=rank, sample_count=spp_rank, sample_stride=world, max_bounce=BOUNCE)
-        if world > 1:
-            dist.reduce(accum_t, dst=0, op=dist.ReduceOp.SUM)
+        ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE)
+        multi_gpu.reduce_accumulator(accum_t, world, dst=0)
         if rank == 0:
             ctx.resolve(A.RESOLVE_TONEMAP_F16, total_samples=SPP)
 
@@ -279,10 +276,11 @@ def run_cuda(args):
                      "tri_tests_per_ray": cst["tri_tests"] / max(1, cst["rays"])},
     }
     if not args.no_cpu_baseline and world == 1:
-        v, dt, cores, kind = cpu_render_rate(desc, cam, 2)
+        cpu_spp = 128  # ~13 s on 15 workers
+        v, dt, cores, kind = cpu_render_rate(desc, cam, cpu_spp)
         line["cpu_baseline"] = {"value": v, "unit": "Mpaths/s", "cores": cores,
                                 "kind": "reference" if kind == "reference" else "port",
-                                "sample": f"2 spp of {SPP} at {WIDTH}x{HEIGHT} ({dt:.1f} s), linear in spp"}
+                                "sample": f"{cpu_spp} spp of {SPP} at {WIDTH}x{HEIGHT} ({dt:.1f} s), linear in spp"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
