@@ -125,11 +125,27 @@ __device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y 
 __device__ __forceinline__ V3 cmul(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 __device__ __forceinline__ float sqnorm(V3 a) { return a.x * a.x + (a.y * a.y + a.z * a.z); }
-__device__ __forceinline__ float norm(V3 a) { return sqrtf(sqnorm(a)); }
+// sqrtf(0) and 0/x leave the inlined fast paths of CUDA's IEEE sqrt and division (FCHK flags a zero operand) and call
+// a ~50-instruction subroutine at the far end of the kernel: ncu showed 1.9 M such calls per 16-spp frame from
+// norm(emissive = 0) and 1.3-1.9 M per component from normalizing axis-aligned vectors (floor normal (0,0,1)), each an
+// instruction-cache miss. The guards below return the same bits (sqrt(+0) = +0; (+-0)/n = +-0 for n > 0) without it.
+__device__ __forceinline__ float norm(V3 a)
+{
+    float sq = sqnorm(a);
+    return sq > 0.f ? sqrtf(sq) : sq; // sq is +0 or NaN otherwise: sqrt(+0) = +0, sqrt(NaN) = NaN
+}
+__device__ __forceinline__ float div_by_norm(float a, float n, bool n_pos)
+{
+    const bool zero = a == 0.f && n_pos;
+    float q = (zero ? n : a) / n;
+    return zero ? a : q;
+}
 __device__ __forceinline__ V3 normalized(V3 a)
 {
-    float n = sqrtf(sqnorm(a));
-    return mk(a.x / n, a.y / n, a.z / n);
+    float sq = sqnorm(a);
+    float n = sq > 0.f ? sqrtf(sq) : sq;
+    const bool n_pos = n > 0.f; // false for the zero vector (0/0 = NaN must stay NaN) and for NaN
+    return mk(div_by_norm(a.x, n, n_pos), div_by_norm(a.y, n, n_pos), div_by_norm(a.z, n, n_pos));
 }
 __device__ __forceinline__ V3 cross(V3 a, V3 b)
 {

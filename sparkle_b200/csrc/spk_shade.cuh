@@ -27,9 +27,16 @@ constexpr float kTolerance = 1e-4f;
 constexpr float kPi = 3.14159274101257324f;      // std::numbers::pi_v<float>
 constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<float>
 
-__device__ __forceinline__ float ref_sin(float x) { return (float)sin((double)x); }
-__device__ __forceinline__ float ref_cos(float x) { return (float)cos((double)x); }
-__device__ __forceinline__ float ref_pow(float x, float y) { return (float)pow((double)x, (double)y); }
+// One out-of-line copy each: the double-precision bodies are 100-500 instructions and were inlined at every call site
+// (three sin/cos pairs, fourteen pow), most of a 108 KiB kernel against a 32 KiB instruction cache.
+__device__ __noinline__ void ref_sincos(float x, float *s, float *c)
+{
+    double ds, dc;
+    sincos((double)x, &ds, &dc); // same values as sin() and cos(): both are correctly rounded to < 1 ulp in double
+    *s = (float)ds;
+    *c = (float)dc;
+}
+__device__ __noinline__ float ref_pow(float x, float y) { return (float)pow((double)x, (double)y); }
 // std::pow(x, 5.f): exact product in double, one rounding
 __device__ __forceinline__ float ref_pow5(float x)
 {
@@ -83,23 +90,77 @@ __device__ __forceinline__ void unit_disk(Rng &r, float &x, float &y)
     float rand = rng_unit(r);
     float theta = rng_unit(r) * 2.0f * kPi;
     float rad = sqrtf(rand);
-    x = rad * ref_cos(theta);
-    y = rad * ref_sin(theta);
+    float sn, cs;
+    ref_sincos(theta, &sn, &cs);
+    x = rad * cs;
+    y = rad * sn;
 }
 
 // ---- textures: Image2D::Sample ----
+// utilities::WrapMod (Utilities.h:526-529): ((unsigned)(a % (int)b) + b) % b is the mathematical a mod b for every
+// int a (the unsigned wrap cancels); one signed remainder and a conditional add give the same value
 __device__ __forceinline__ uint32_t wrap_mod(int a, uint32_t b)
 {
-    return ((uint32_t)(a % (int)b) + b) % b;
+    int m = a % (int)b;
+    return (uint32_t)(m < 0 ? m + (int)b : m);
 }
+
+// ColorToVec = cast<float>() / 255.f (io/Image.h:60-110): the 256 possible IEEE quotients float(k) / 255.f as exact
+// hex-float literals (generated with numpy float32 division; tests/test_render_gpu.py checks the texture path against the
+// reference), instead of 16 inlined division sequences per bilinear sample
+static __device__ const float g_unorm8[256] = {
+    0x0.0p+0f, 0x1.0101020000000p-8f, 0x1.0101020000000p-7f, 0x1.8181820000000p-7f, 0x1.0101020000000p-6f, 0x1.4141420000000p-6f,
+    0x1.8181820000000p-6f, 0x1.c1c1c20000000p-6f, 0x1.0101020000000p-5f, 0x1.2121220000000p-5f, 0x1.4141420000000p-5f, 0x1.6161620000000p-5f,
+    0x1.8181820000000p-5f, 0x1.a1a1a20000000p-5f, 0x1.c1c1c20000000p-5f, 0x1.e1e1e20000000p-5f, 0x1.0101020000000p-4f, 0x1.1111120000000p-4f,
+    0x1.2121220000000p-4f, 0x1.3131320000000p-4f, 0x1.4141420000000p-4f, 0x1.5151520000000p-4f, 0x1.6161620000000p-4f, 0x1.7171720000000p-4f,
+    0x1.8181820000000p-4f, 0x1.9191920000000p-4f, 0x1.a1a1a20000000p-4f, 0x1.b1b1b20000000p-4f, 0x1.c1c1c20000000p-4f, 0x1.d1d1d20000000p-4f,
+    0x1.e1e1e20000000p-4f, 0x1.f1f1f20000000p-4f, 0x1.0101020000000p-3f, 0x1.09090a0000000p-3f, 0x1.1111120000000p-3f, 0x1.19191a0000000p-3f,
+    0x1.2121220000000p-3f, 0x1.29292a0000000p-3f, 0x1.3131320000000p-3f, 0x1.39393a0000000p-3f, 0x1.4141420000000p-3f, 0x1.49494a0000000p-3f,
+    0x1.5151520000000p-3f, 0x1.59595a0000000p-3f, 0x1.6161620000000p-3f, 0x1.69696a0000000p-3f, 0x1.7171720000000p-3f, 0x1.79797a0000000p-3f,
+    0x1.8181820000000p-3f, 0x1.89898a0000000p-3f, 0x1.9191920000000p-3f, 0x1.99999a0000000p-3f, 0x1.a1a1a20000000p-3f, 0x1.a9a9aa0000000p-3f,
+    0x1.b1b1b20000000p-3f, 0x1.b9b9ba0000000p-3f, 0x1.c1c1c20000000p-3f, 0x1.c9c9ca0000000p-3f, 0x1.d1d1d20000000p-3f, 0x1.d9d9da0000000p-3f,
+    0x1.e1e1e20000000p-3f, 0x1.e9e9ea0000000p-3f, 0x1.f1f1f20000000p-3f, 0x1.f9f9fa0000000p-3f, 0x1.0101020000000p-2f, 0x1.0505060000000p-2f,
+    0x1.09090a0000000p-2f, 0x1.0d0d0e0000000p-2f, 0x1.1111120000000p-2f, 0x1.1515160000000p-2f, 0x1.19191a0000000p-2f, 0x1.1d1d1e0000000p-2f,
+    0x1.2121220000000p-2f, 0x1.2525260000000p-2f, 0x1.29292a0000000p-2f, 0x1.2d2d2e0000000p-2f, 0x1.3131320000000p-2f, 0x1.3535360000000p-2f,
+    0x1.39393a0000000p-2f, 0x1.3d3d3e0000000p-2f, 0x1.4141420000000p-2f, 0x1.4545460000000p-2f, 0x1.49494a0000000p-2f, 0x1.4d4d4e0000000p-2f,
+    0x1.5151520000000p-2f, 0x1.5555560000000p-2f, 0x1.59595a0000000p-2f, 0x1.5d5d5e0000000p-2f, 0x1.6161620000000p-2f, 0x1.6565660000000p-2f,
+    0x1.69696a0000000p-2f, 0x1.6d6d6e0000000p-2f, 0x1.7171720000000p-2f, 0x1.7575760000000p-2f, 0x1.79797a0000000p-2f, 0x1.7d7d7e0000000p-2f,
+    0x1.8181820000000p-2f, 0x1.8585860000000p-2f, 0x1.89898a0000000p-2f, 0x1.8d8d8e0000000p-2f, 0x1.9191920000000p-2f, 0x1.9595960000000p-2f,
+    0x1.99999a0000000p-2f, 0x1.9d9d9e0000000p-2f, 0x1.a1a1a20000000p-2f, 0x1.a5a5a60000000p-2f, 0x1.a9a9aa0000000p-2f, 0x1.adadae0000000p-2f,
+    0x1.b1b1b20000000p-2f, 0x1.b5b5b60000000p-2f, 0x1.b9b9ba0000000p-2f, 0x1.bdbdbe0000000p-2f, 0x1.c1c1c20000000p-2f, 0x1.c5c5c60000000p-2f,
+    0x1.c9c9ca0000000p-2f, 0x1.cdcdce0000000p-2f, 0x1.d1d1d20000000p-2f, 0x1.d5d5d60000000p-2f, 0x1.d9d9da0000000p-2f, 0x1.ddddde0000000p-2f,
+    0x1.e1e1e20000000p-2f, 0x1.e5e5e60000000p-2f, 0x1.e9e9ea0000000p-2f, 0x1.ededee0000000p-2f, 0x1.f1f1f20000000p-2f, 0x1.f5f5f60000000p-2f,
+    0x1.f9f9fa0000000p-2f, 0x1.fdfdfe0000000p-2f, 0x1.0101020000000p-1f, 0x1.0303040000000p-1f, 0x1.0505060000000p-1f, 0x1.0707080000000p-1f,
+    0x1.09090a0000000p-1f, 0x1.0b0b0c0000000p-1f, 0x1.0d0d0e0000000p-1f, 0x1.0f0f100000000p-1f, 0x1.1111120000000p-1f, 0x1.1313140000000p-1f,
+    0x1.1515160000000p-1f, 0x1.1717180000000p-1f, 0x1.19191a0000000p-1f, 0x1.1b1b1c0000000p-1f, 0x1.1d1d1e0000000p-1f, 0x1.1f1f200000000p-1f,
+    0x1.2121220000000p-1f, 0x1.2323240000000p-1f, 0x1.2525260000000p-1f, 0x1.2727280000000p-1f, 0x1.29292a0000000p-1f, 0x1.2b2b2c0000000p-1f,
+    0x1.2d2d2e0000000p-1f, 0x1.2f2f300000000p-1f, 0x1.3131320000000p-1f, 0x1.3333340000000p-1f, 0x1.3535360000000p-1f, 0x1.3737380000000p-1f,
+    0x1.39393a0000000p-1f, 0x1.3b3b3c0000000p-1f, 0x1.3d3d3e0000000p-1f, 0x1.3f3f400000000p-1f, 0x1.4141420000000p-1f, 0x1.4343440000000p-1f,
+    0x1.4545460000000p-1f, 0x1.4747480000000p-1f, 0x1.49494a0000000p-1f, 0x1.4b4b4c0000000p-1f, 0x1.4d4d4e0000000p-1f, 0x1.4f4f500000000p-1f,
+    0x1.5151520000000p-1f, 0x1.5353540000000p-1f, 0x1.5555560000000p-1f, 0x1.5757580000000p-1f, 0x1.59595a0000000p-1f, 0x1.5b5b5c0000000p-1f,
+    0x1.5d5d5e0000000p-1f, 0x1.5f5f600000000p-1f, 0x1.6161620000000p-1f, 0x1.6363640000000p-1f, 0x1.6565660000000p-1f, 0x1.6767680000000p-1f,
+    0x1.69696a0000000p-1f, 0x1.6b6b6c0000000p-1f, 0x1.6d6d6e0000000p-1f, 0x1.6f6f700000000p-1f, 0x1.7171720000000p-1f, 0x1.7373740000000p-1f,
+    0x1.7575760000000p-1f, 0x1.7777780000000p-1f, 0x1.79797a0000000p-1f, 0x1.7b7b7c0000000p-1f, 0x1.7d7d7e0000000p-1f, 0x1.7f7f800000000p-1f,
+    0x1.8181820000000p-1f, 0x1.8383840000000p-1f, 0x1.8585860000000p-1f, 0x1.8787880000000p-1f, 0x1.89898a0000000p-1f, 0x1.8b8b8c0000000p-1f,
+    0x1.8d8d8e0000000p-1f, 0x1.8f8f900000000p-1f, 0x1.9191920000000p-1f, 0x1.9393940000000p-1f, 0x1.9595960000000p-1f, 0x1.9797980000000p-1f,
+    0x1.99999a0000000p-1f, 0x1.9b9b9c0000000p-1f, 0x1.9d9d9e0000000p-1f, 0x1.9f9fa00000000p-1f, 0x1.a1a1a20000000p-1f, 0x1.a3a3a40000000p-1f,
+    0x1.a5a5a60000000p-1f, 0x1.a7a7a80000000p-1f, 0x1.a9a9aa0000000p-1f, 0x1.ababac0000000p-1f, 0x1.adadae0000000p-1f, 0x1.afafb00000000p-1f,
+    0x1.b1b1b20000000p-1f, 0x1.b3b3b40000000p-1f, 0x1.b5b5b60000000p-1f, 0x1.b7b7b80000000p-1f, 0x1.b9b9ba0000000p-1f, 0x1.bbbbbc0000000p-1f,
+    0x1.bdbdbe0000000p-1f, 0x1.bfbfc00000000p-1f, 0x1.c1c1c20000000p-1f, 0x1.c3c3c40000000p-1f, 0x1.c5c5c60000000p-1f, 0x1.c7c7c80000000p-1f,
+    0x1.c9c9ca0000000p-1f, 0x1.cbcbcc0000000p-1f, 0x1.cdcdce0000000p-1f, 0x1.cfcfd00000000p-1f, 0x1.d1d1d20000000p-1f, 0x1.d3d3d40000000p-1f,
+    0x1.d5d5d60000000p-1f, 0x1.d7d7d80000000p-1f, 0x1.d9d9da0000000p-1f, 0x1.dbdbdc0000000p-1f, 0x1.ddddde0000000p-1f, 0x1.dfdfe00000000p-1f,
+    0x1.e1e1e20000000p-1f, 0x1.e3e3e40000000p-1f, 0x1.e5e5e60000000p-1f, 0x1.e7e7e80000000p-1f, 0x1.e9e9ea0000000p-1f, 0x1.ebebec0000000p-1f,
+    0x1.ededee0000000p-1f, 0x1.efeff00000000p-1f, 0x1.f1f1f20000000p-1f, 0x1.f3f3f40000000p-1f, 0x1.f5f5f60000000p-1f, 0x1.f7f7f80000000p-1f,
+    0x1.f9f9fa0000000p-1f, 0x1.fbfbfc0000000p-1f, 0x1.fdfdfe0000000p-1f, 0x1.0000000000000p+0f,
+};
 
 __device__ __forceinline__ float4 access_pixel(const DTexture &t, uint32_t x, uint32_t y)
 {
     size_t idx = size_t(y) * t.width + x;
-    if (t.format <= 1u) // RGBA8 unorm / srgb: ColorToVec = cast<float>() / 255.f
+    if (t.format <= 1u) // RGBA8 unorm / srgb
     {
         uchar4 c = __ldg(reinterpret_cast<const uchar4 *>(t.pixels) + idx);
-        return make_float4((float)c.x / 255.f, (float)c.y / 255.f, (float)c.z / 255.f, (float)c.w / 255.f);
+        return make_float4(g_unorm8[c.x], g_unorm8[c.y], g_unorm8[c.z], g_unorm8[c.w]);
     }
     if (t.format == 2u) // RGBAFloat16
     {
@@ -121,13 +182,14 @@ __device__ __forceinline__ float srgb_to_linear(float c)
     return higher * (1.f - cutoff) + lower * cutoff;
 }
 
-__device__ __forceinline__ V3 sample_texture(const DTexture &t, float u, float v)
+__device__ __noinline__ V3 sample_texture(const DTexture &t, float u, float v)
 {
     float px = u * (float)(t.width - 1), py = v * (float)(t.height - 1);
     int ui = (int)px, vi = (int)py; // utilities::Decompose: truncation toward zero
     float uc = px - (float)ui, vc = py - (float)vi;
-    uint32_t x0 = wrap_mod(ui, t.width), x1 = wrap_mod(ui + 1, t.width);
-    uint32_t y0 = wrap_mod(vi, t.height), y1 = wrap_mod(vi + 1, t.height);
+    // WrapMod(ui + 1) = (WrapMod(ui) + 1) mod width: a compare instead of a second remainder
+    uint32_t x0 = wrap_mod(ui, t.width), x1 = x0 + 1u == t.width ? 0u : x0 + 1u;
+    uint32_t y0 = wrap_mod(vi, t.height), y1 = y0 + 1u == t.height ? 0u : y0 + 1u;
     float4 s00 = access_pixel(t, x0, y0), s10 = access_pixel(t, x1, y0);
     float4 s01 = access_pixel(t, x0, y1), s11 = access_pixel(t, x1, y1);
     float r0 = lerp1(s00.x, s10.x, uc), g0 = lerp1(s00.y, s10.y, uc), b0 = lerp1(s00.z, s10.z, uc);
@@ -306,7 +368,9 @@ __device__ __forceinline__ V3 sample_vndf(Rng &rng, V3 wo, float roughness)
     V3 t2 = cross(v, t1);
     float r = sqrtf(u1);
     float phi = 2.f * kPi * u2;
-    float p1 = r * ref_cos(phi), p2 = r * ref_sin(phi);
+    float sn, cs;
+    ref_sincos(phi, &sn, &cs);
+    float p1 = r * cs, p2 = r * sn;
     float s = 0.5f * (1.f + v.z);
     p2 = (1.f - s) * sqrtf(1.f - p1 * p1) + s * p2;
     float c = sqrtf(fmaxf(0.f, 1.f - p1 * p1 - p2 * p2));
