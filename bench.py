@@ -270,7 +270,7 @@ def run_cuda(args):
                 "ms_per_step": ms_e2e / e2e_steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "render_kernel<CULL=true>",
+                     "traffic": None, "peak_source": peak_src, "kernel": "render_phased_kernel<CULL=true, 8 warps x 3 CTAs/SM>",
                      "alg_bytes_per_ray": alg_bytes / max(1.0, rays_launch),
                      "node_visits_per_ray": cst["node_visits"] / max(1, cst["rays"]),
                      "tri_tests_per_ray": cst["tri_tests"] / max(1, cst["rays"])},

@@ -15,6 +15,8 @@
  * Compiled with -fmad=false (spk_device.cuh).
  */
 #include "spk_context.h"
+
+#include <cstdlib>
 #include "spk_shade.cuh"
 #include "spk_traverse.cuh"
 
@@ -161,6 +163,202 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
     }
 }
 
+
+// ---- phased form: the same per-pixel loop, but the CTA walks through it in lock step ----
+// ncu on render_kernel: 64-68 % of warp-stall samples are `no_instruction` — 28 warps per SM, each somewhere else in a
+// 66 KiB program, against a 32 KiB L1.5 instruction cache. Here every iteration has three phases separated by CTA
+// barriers — (A) start the next sample where a path just ended, (B) trace one segment, (C) shade it — so all warps of
+// a CTA fetch the same few KiB at the same time. Per-pixel arithmetic and the order samples are added are unchanged.
+template <bool CULL, bool COUNT, int WARPS, int MINB, bool SYNC2>
+__global__ void __launch_bounds__(WARPS * 32, MINB)
+    render_phased_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
+                         unsigned long long *__restrict__ counters)
+{
+    const uint32_t tiles_x = (a.width + kTileW - 1) / kTileW;
+    const uint32_t warp = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t i = (warp % tiles_x) * kTileW + (lane & (kTileW - 1));
+    const uint32_t j = (warp / tiles_x) * kTileH + (lane / kTileW);
+    const bool in_image = i < a.width && j < a.height;
+    uint32_t rays = 0;
+    TraceCounters cnt{0, 0, 0, 0};
+    const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
+    const V3 cpos = mk(cam.position[0], cam.position[1], cam.position[2]);
+    const V3 cup = mk(cam.up[0], cam.up[1], cam.up[2]);
+    const V3 cright = mk(cam.right[0], cam.right[1], cam.right[2]);
+    const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
+    const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
+    const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (in_image)
+    {
+        acc = accum[size_t(j) * a.width + i];
+    }
+    uint32_t stack[64];
+    uint32_t s = 0, bounce = 0;
+    bool live = in_image, need_path = true;
+    Rng rng;
+    V3 origin, dir, throughput, color;
+    float valid = 1.f;
+    for (;;)
+    {
+        // ---- phase A: next sample of this pixel
+        if (live && need_path)
+        {
+            if (s >= a.sample_count)
+            {
+                live = false;
+            }
+            else
+            {
+                    // CPURenderer.cpp:442-443, unsigned wrap
+                    const uint32_t frame_seed = a.first_sample + s * a.sample_stride;
+                    rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+                    float u = ((float)i + rng_unit(rng)) * pw;
+                    float v = ((float)j + rng_unit(rng)) * ph;
+                    // SetupViewRay
+                    float dx, dy;
+                    unit_disk(rng, dx, dy);
+                    dx = dx * cam.aperture_radius;
+                    dy = dy * cam.aperture_radius;
+                    origin = cpos + (dx * cright + dy * cup);
+                    V3 target = lower_left + u * max_u + v * max_v;
+                    dir = normalized(target - origin);
+                    throughput = mk(1.f, 1.f, 1.f);
+                    color = mk(0.f, 0.f, 0.f);
+                    valid = 1.f;
+                    bounce = 0;
+need_path = false;
+            }
+        }
+        if (!__syncthreads_or(live))
+        {
+            break;
+        }
+        // ---- phase B: one path segment
+        bool done = false;
+            Hit hit;
+            hit.inst = SPK_INVALID_ID;
+            if (live && a.max_bounce != 0u)
+            {
+                trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
+                rays++;
+            }
+        if (SYNC2)
+        {
+            __syncthreads();
+        }
+        // ---- phase C: shade it
+        if (live)
+        {
+                if (a.max_bounce == 0u)
+                {
+                    done = true; // a zero-iteration bounce loop: the sample is black and valid
+                }
+                else if (hit.inst == SPK_INVALID_ID)
+                {
+                    if (sc.sky.has_sky)
+                    {
+                        color = color + cmul(sky_evaluate(sc, dir), throughput);
+                    }
+                    done = true;
+                }
+                else
+                {
+                    Surface sf;
+                    get_intersection(sc, origin, dir, hit, sf);
+                    V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
+                    if (a.debug)
+                    {
+                        // parity probes (tests only): first-hit normal / tangent / (u, v, t)
+                        color = a.debug == 1 ? sf.normal : a.debug == 2 ? sf.tangent : mk(sf.u, sf.v, hit.t);
+                        done = true;
+                    }
+                    else if (norm(emissive) > kEps)
+                    {
+                        color = color + cmul(emissive, throughput);
+                        done = true;
+                    }
+                    else
+                    {
+                        V3 next_dir;
+                        V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
+                        throughput = cmul(throughput, this_throughput);
+                        if (sqnorm(throughput) < kEps)
+                        {
+                            valid = -1.f;
+                            done = true;
+                        }
+                        else
+                        {
+                            if (bounce >= 3)
+                            {
+                                float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
+                                p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
+                                if (rng_unit(rng) > p)
+                                {
+                                    done = true;
+                                }
+                                else
+                                {
+                                    throughput = throughput / p;
+                                }
+                            }
+                            if (!done)
+                            {
+                                origin = sf.location + next_dir * kTolerance;
+                                dir = next_dir;
+                                bounce++;
+                                done = bounce >= a.max_bounce; // the bounce cap adds nothing (CPURenderer.cpp:256)
+                            }
+                        }
+                    }
+                }
+                if (done)
+                {
+                    color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
+                    if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
+                    {
+                        uint32_t n = a.cumulated + s;
+                        float ma = (float)n / (float)(n + 1u);
+                        acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
+                                          lerp1(valid, acc.w, ma));
+                    }
+                    else
+                    {
+                        acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
+                    }
+                    s++;
+                    need_path = true;
+                }
+        }
+    }
+    if (in_image)
+    {
+        accum[size_t(j) * a.width + i] = acc;
+    }
+    uint32_t total = __reduce_add_sync(0xffffffffu, rays);
+    uint32_t pixels = __popc(__ballot_sync(0xffffffffu, in_image));
+    if (lane == 0 && pixels)
+    {
+        atomicAdd(counters + 0, (unsigned long long)pixels * a.sample_count);
+        atomicAdd(counters + 1, (unsigned long long)total);
+    }
+    if (COUNT)
+    {
+        uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+        {
+            uint32_t sum = __reduce_add_sync(0xffffffffu, v[k]);
+            if (lane == 0 && sum)
+            {
+                atomicAdd(counters + 2 + k, (unsigned long long)sum);
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ float aces(float c)
 {
     // ACESFilm (CPURenderer.cpp:554-563): clamp((c(2.51c+0.03))/(c(2.43c+0.59)+0.14), 0, 1)
@@ -224,9 +422,46 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
     a.cumulated = ctx->accum_samples;
     a.debug = (p->flags >> 8) & 3u;
     uint32_t tiles = ((a.width + kTileW - 1) / kTileW) * ((a.height + kTileH - 1) / kTileH);
-    dim3 grid{(tiles + kWarpsPerBlock - 1) / kWarpsPerBlock}, block{kWarpsPerBlock * 32};
     const DScene &scene = ctx->scene;
     const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
+    static const int phased = [] {
+        const char *e = getenv("SPK_RENDER_PHASED");
+        return e ? atoi(e) : 831; // default: 8 warps per CTA, 3 CTAs per SM, both barriers (measured best)
+    }();
+    if (phased != 0)
+    {
+        // SPK_RENDER_PHASED = warps*100 + min_blocks*10 + second_barrier selects a measured variant; 0 = render_kernel
+#define SPK_PHASED_CASE(W, B, S2)                                                                                      \
+    case W * 100 + B * 10 + S2:                                                                                        \
+        if (!exact && !count)                                                                                          \
+            render_phased_kernel<true, false, W, B, S2 != 0>                                                           \
+                <<<(tiles + W - 1) / W, W * 32, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+        else if (exact && !count)                                                                                      \
+            render_phased_kernel<false, false, W, B, S2 != 0>                                                          \
+                <<<(tiles + W - 1) / W, W * 32, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+        else if (!exact)                                                                                               \
+            render_phased_kernel<true, true, W, B, S2 != 0>                                                            \
+                <<<(tiles + W - 1) / W, W * 32, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+        else                                                                                                           \
+            render_phased_kernel<false, true, W, B, S2 != 0>                                                           \
+                <<<(tiles + W - 1) / W, W * 32, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+        break;
+        switch (phased)
+        {
+            SPK_PHASED_CASE(8, 3, 1)
+            SPK_PHASED_CASE(8, 3, 0)
+            SPK_PHASED_CASE(16, 2, 1)
+            SPK_PHASED_CASE(4, 6, 1)
+        default:
+            set_error("spk_cuda_render: unknown SPK_RENDER_PHASED variant");
+            return SPK_ERR_INVALID_ARGUMENT;
+        }
+#undef SPK_PHASED_CASE
+        SPK_CUDA_TRY(cudaGetLastError());
+        ctx->stats.kernel_launches++;
+        return SPK_OK;
+    }
+    dim3 grid{(tiles + kWarpsPerBlock - 1) / kWarpsPerBlock}, block{kWarpsPerBlock * 32};
 #define SPK_LAUNCH_RENDER(C, N)                                                                                        \
     render_kernel<C, N><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters)
     if (exact && count)

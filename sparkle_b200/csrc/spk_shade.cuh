@@ -80,8 +80,9 @@ __device__ __forceinline__ float rng_unit(Rng &r)
     r.s0 ^= r.s3;
     r.s2 ^= t;
     r.s3 = (r.s3 << 11) | (r.s3 >> 21);
-    // static_cast<float>(r) / static_cast<float>(UINT32_MAX): both round to nearest; 1.0f is reachable
-    return __uint2float_rn(result) / 4294967296.0f;
+    // static_cast<float>(r) / static_cast<float>(UINT32_MAX): both round to nearest, the divisor is 2^32, and 1.0f is
+    // reachable. Dividing by 2^32 and multiplying by 2^-32 are the same exact exponent shift (no result is subnormal).
+    return __uint2float_rn(result) * 2.3283064365386962890625e-10f;
 }
 
 // sampler::UnitDisk: rand, then theta = (u * 2.0f) * Pi

@@ -17,9 +17,9 @@ if what in ("both", "render"):
     ctx.set_camera(orbit_camera(w, h, **camkw))
     for k in range(2):
         ctx.reset_accumulation()
-        ctx.render(0, 16, max_bounce=8)
+        ctx.render(0, int(os.environ.get("SPK_SPP", 16)), max_bounce=8)
         ctx.synchronize()
-        print("render 16 spp ms", ctx.stats()["last_ms"])
+        print("render spp ms", ctx.stats()["last_ms"])
     ctx.close()
 if what in ("both", "trace"):
     n_tris = int(os.environ.get("SPK_TRIS", 1_000_000))
