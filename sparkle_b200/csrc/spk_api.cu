@@ -276,6 +276,7 @@ int spk_cuda_destroy(SpkContext *ctx)
     cudaFree(ctx->d_rays);
     cudaFree(ctx->d_hits);
     cudaFree(ctx->d_resolve);
+    cudaFree(ctx->wf_block);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream)

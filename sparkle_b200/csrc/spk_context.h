@@ -44,6 +44,10 @@ struct SpkContext
 
     void *d_resolve = nullptr;
     size_t resolve_capacity = 0;
+
+    // wavefront tracer: path-slot pool (spk_wavefront.cu)
+    void *wf_block = nullptr;
+    uint32_t wf_slots = 0;
 };
 
 namespace spk
@@ -61,5 +65,6 @@ int cuda_fail(cudaError_t e, const char *what);
 // kernels (spk_trace.cu / spk_render.cu)
 int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags);
 int launch_render(SpkContext *ctx, const SpkRenderParams *params);
+int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *params);
 int launch_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, uint32_t accum_mode, void *d_out);
 } // namespace spk

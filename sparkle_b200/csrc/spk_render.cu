@@ -505,11 +505,6 @@ int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params)
         set_error("spk_cuda_render: bad accum_mode or output_limit");
         return SPK_ERR_INVALID_ARGUMENT;
     }
-    if (params->flags & SPK_FLAG_WAVEFRONT)
-    {
-        set_error("spk_cuda_render: the wavefront tracer is not built; the megakernel is the measured choice");
-        return SPK_ERR_UNSUPPORTED;
-    }
     if (ctx->accum_samples != 0 && params->accum_mode != ctx->accum_mode)
     {
         set_error("spk_cuda_render: accum_mode changed without spk_cuda_reset_accumulation");
@@ -521,7 +516,9 @@ int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params)
     }
     SPK_CUDA_TRY(cudaSetDevice(ctx->device));
     SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
-    int rc = launch_render(ctx, params);
+    // a zero-iteration bounce loop has nothing to queue: the megakernel handles it
+    const bool wavefront = (params->flags & SPK_FLAG_WAVEFRONT) && params->max_bounce != 0u;
+    int rc = wavefront ? launch_render_wavefront(ctx, params) : launch_render(ctx, params);
     if (rc != SPK_OK)
     {
         return rc;

@@ -29,14 +29,14 @@ constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<
 
 // One out-of-line copy each: the double-precision bodies are 100-500 instructions and were inlined at every call site
 // (three sin/cos pairs, fourteen pow), most of a 108 KiB kernel against a 32 KiB instruction cache.
-__device__ __noinline__ void ref_sincos(float x, float *s, float *c)
+static __device__ __noinline__ void ref_sincos(float x, float *s, float *c)
 {
     double ds, dc;
     sincos((double)x, &ds, &dc); // same values as sin() and cos(): both are correctly rounded to < 1 ulp in double
     *s = (float)ds;
     *c = (float)dc;
 }
-__device__ __noinline__ float ref_pow(float x, float y) { return (float)pow((double)x, (double)y); }
+static __device__ __noinline__ float ref_pow(float x, float y) { return (float)pow((double)x, (double)y); }
 // std::pow(x, 5.f): exact product in double, one rounding
 __device__ __forceinline__ float ref_pow5(float x)
 {
@@ -183,7 +183,7 @@ __device__ __forceinline__ float srgb_to_linear(float c)
     return higher * (1.f - cutoff) + lower * cutoff;
 }
 
-__device__ __noinline__ V3 sample_texture(const DTexture &t, float u, float v)
+static __device__ __noinline__ V3 sample_texture(const DTexture &t, float u, float v)
 {
     float px = u * (float)(t.width - 1), py = v * (float)(t.height - 1);
     int ui = (int)px, vi = (int)py; // utilities::Decompose: truncation toward zero

@@ -1,0 +1,555 @@
+/*
+ * spk_wavefront.cu — wavefront (queue) form of the path tracer, selected by SPK_FLAG_WAVEFRONT.
+ *
+ * Same per-sample arithmetic as render_kernel (spk_render.cu; CPURenderer.cpp:220-450): every (pixel, sample) path draws
+ * from the same seeded stream and runs the same device functions, so each sample's radiance is bit-identical to the
+ * megakernel's; only the ORDER in which samples are added to a pixel differs (vector float atomics), i.e. float
+ * association of the sum (~1e-7 relative). SPK_ACCUM_SUM only.
+ *
+ * A pool of P path slots lives in HBM/L2 (84 B per slot: ray 32 B carrying pixel + bounce in its pad words, hit 20 B,
+ * rng 16 B, throughput 16 B). One iteration = four launches, no host round trip (counts live in a device control block):
+ *   wf_shade    one thread per traced slot. The CTA first sorts its 256 slots by material class in shared memory
+ *               (miss / sphere|mesh x pbr|dielectric x textured x emissive), so a warp shades like with like.
+ *               Continuing paths are appended to the next ray queue, finished ones to the regen list
+ *               (warp-ballot compaction, one atomic per warp).
+ *   wf_regen    finished slots take the next (pixel, sample) work items in order: consecutive threads get consecutive
+ *               pixels of a row, so new primary rays enter the queue as coherent runs.
+ *   wf_advance  one thread: rotates the counters.
+ *   wf_extend   persistent warp-voting traversal (spk_traverse_warp.cuh) over the ray queue: lanes refill from the
+ *               queue, so warps stay full however long individual rays take.
+ */
+#include "spk_context.h"
+
+#include <cstdlib>
+#include "spk_shade.cuh"
+#include "spk_traverse.cuh"
+#include "spk_traverse_warp.cuh"
+
+namespace spk
+{
+namespace
+{
+constexpr int kShadeThreads = 256;
+constexpr int kExtendWarps = 4;
+constexpr uint32_t kEmptySlot = 0xFFFFFFFFu;
+
+struct WfCtrl
+{
+    uint32_t n_queue[2]; // entries in queue[0] / queue[1]
+    uint32_t n_regen;    // entries in the regen list
+    uint32_t next_ray;   // wf_extend's queue cursor
+    unsigned long long work_next, work_total; // (pixel, sample) items handed out so far / in this call
+    unsigned long long rays;                   // segments traced in this call
+};
+
+struct WfState
+{
+    float4 *rays;    // 2 per slot: {origin.xyz, pixel bits}, {direction.xyz, bounce bits}
+    float4 *hit;     // {t, u, v, instance slot bits}
+    uint32_t *face;
+    uint4 *rng;
+    float4 *thr;     // throughput.xyz
+    uint32_t *queue[2];
+    uint32_t *regen;
+    WfCtrl *ctrl;
+    uint32_t slots;
+};
+
+struct WfArgs
+{
+    uint32_t width, height;
+    uint32_t first_sample, sample_stride, max_bounce;
+    float output_limit;
+};
+
+__global__ void wf_init_kernel(WfState st, unsigned long long total)
+{
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < st.slots)
+    {
+        st.regen[k] = k;
+        st.rays[2 * size_t(k)].w = __uint_as_float(kEmptySlot);
+    }
+    if (k == 0)
+    {
+        WfCtrl c;
+        c.n_queue[0] = c.n_queue[1] = 0;
+        c.n_regen = st.slots;
+        c.next_ray = 0;
+        c.work_next = 0;
+        c.work_total = total;
+        c.rays = 0;
+        *st.ctrl = c;
+    }
+}
+
+// RenderPixel + SetupViewRay (CPURenderer.cpp:398-417, 220-238) for work item w = sample * W*H + pixel
+__global__ void __launch_bounds__(kShadeThreads)
+    wf_regen_kernel(const DCamera cam, const WfArgs a, WfState st, uint32_t nxt)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    const WfCtrl c = *st.ctrl;
+    if (k >= c.n_regen)
+    {
+        return;
+    }
+    const uint32_t slot = st.regen[k];
+    const unsigned long long w = c.work_next + k;
+    if (w >= c.work_total)
+    {
+        st.rays[2 * size_t(slot)].w = __uint_as_float(kEmptySlot);
+        return;
+    }
+    const uint32_t npix = a.width * a.height;
+    const uint32_t s = uint32_t(w / npix), p = uint32_t(w % npix);
+    const uint32_t i = p % a.width, j = p / a.width;
+    const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
+    const uint32_t frame_seed = a.first_sample + s * a.sample_stride; // CPURenderer.cpp:442-443, unsigned wrap
+    Rng rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+    float u = ((float)i + rng_unit(rng)) * pw;
+    float v = ((float)j + rng_unit(rng)) * ph;
+    float dx, dy;
+    unit_disk(rng, dx, dy);
+    dx = dx * cam.aperture_radius;
+    dy = dy * cam.aperture_radius;
+    const V3 cpos = mk(cam.position[0], cam.position[1], cam.position[2]);
+    const V3 cup = mk(cam.up[0], cam.up[1], cam.up[2]);
+    const V3 cright = mk(cam.right[0], cam.right[1], cam.right[2]);
+    const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
+    const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
+    const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
+    V3 origin = cpos + (dx * cright + dy * cup);
+    V3 target = lower_left + u * max_u + v * max_v;
+    V3 dir = normalized(target - origin);
+    st.rays[2 * size_t(slot)] = make_float4(origin.x, origin.y, origin.z, __uint_as_float(p));
+    st.rays[2 * size_t(slot) + 1] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(0u));
+    st.rng[slot] = make_uint4(rng.s0, rng.s1, rng.s2, rng.s3);
+    st.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+    st.queue[nxt][c.n_queue[nxt] + k] = slot; // after the entries wf_shade appended; wf_advance adds the count
+}
+
+__global__ void wf_advance_kernel(WfState st, uint32_t cur, unsigned long long *__restrict__ counters)
+{
+    WfCtrl *c = st.ctrl;
+    const uint32_t nxt = cur ^ 1u;
+    unsigned long long left = c->work_total - c->work_next;
+    unsigned long long gen = c->n_regen < left ? c->n_regen : left;
+    c->n_queue[nxt] += uint32_t(gen);
+    c->work_next += gen;
+    c->n_regen = 0;
+    c->n_queue[cur] = 0;
+    c->next_ray = 0;
+    c->rays += c->n_queue[nxt];
+    counters[0] += gen;               // paths started
+    counters[1] += c->n_queue[nxt];   // segments traced
+}
+
+// ---- extend: closest hit of every queued ray; the loop of trace_persistent_kernel (spk_trace.cu) over an indirect queue
+template <bool CULL, bool COUNT, int LEAF_VOTE>
+__global__ void __launch_bounds__(kExtendWarps * 32)
+    wf_extend_kernel(const DScene sc, WfState st, uint32_t q, unsigned long long *__restrict__ counters)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const uint32_t n = st.ctrl->n_queue[q];
+    const uint32_t *__restrict__ queue = st.queue[q];
+    const float4 *__restrict__ rays = st.rays;
+    uint32_t *next_ray = &st.ctrl->next_ray;
+    uint32_t stack[kWarpStack];
+    LaneState s;
+    TraceCounters cnt{0, 0, 0, 0};
+    uint32_t slot = kEmptySlot;
+    bool active = false;
+    bool exhausted = false; // warp-uniform: the queue cursor has passed n
+    const float4 *__restrict__ pairs = sc.pairs;
+    for (;;)
+    {
+        unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle && exhausted)
+        {
+            if (idle == 0xffffffffu)
+            {
+                break;
+            }
+        }
+        else if (idle)
+        {
+            uint32_t base = 0;
+            int leader = __ffs(idle) - 1;
+            if ((int)lane == leader)
+            {
+                base = atomicAdd(next_ray, (uint32_t)__popc(idle));
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active)
+            {
+                uint32_t id = base + __popc(idle & lt_mask);
+                if (id < n)
+                {
+                    slot = __ldg(queue + id);
+                    float4 ro = rays[2 * size_t(slot)], rd = rays[2 * size_t(slot) + 1];
+                    lane_begin<CULL>(sc, s, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z));
+                    active = true;
+                }
+            }
+            exhausted = base + __popc(idle) >= n;
+            if (base >= n && !__any_sync(0xffffffffu, active))
+            {
+                break;
+            }
+        }
+        for (;;)
+        {
+            bool inner = active && (s.top & 15u) == 0u;
+            unsigned m_inner = __ballot_sync(0xffffffffu, inner);
+            unsigned m_leaf = __ballot_sync(0xffffffffu, active && !inner);
+            if (m_inner == 0u || __popc(m_leaf) >= LEAF_VOTE)
+            {
+                break;
+            }
+            if (inner)
+            {
+                active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
+            }
+        }
+        if (active && (s.top & 15u) != 0u)
+        {
+            active = lane_leaf_step<CULL, COUNT>(sc, s, stack, cnt);
+        }
+        if (!active && slot != kEmptySlot)
+        {
+            st.hit[slot] = make_float4(s.best.t, s.best.u, s.best.v, __uint_as_float(s.best.inst));
+            st.face[slot] = s.best.face;
+            slot = kEmptySlot;
+        }
+    }
+    if (COUNT)
+    {
+        uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+        {
+            uint32_t sum = __reduce_add_sync(0xffffffffu, v[k]);
+            if (lane == 0 && sum)
+            {
+                atomicAdd(counters + 2 + k, (unsigned long long)sum);
+            }
+        }
+    }
+}
+
+// material class of a traced slot: what the warp should be sorted by
+__device__ __forceinline__ uint32_t shade_class(const DScene &sc, uint32_t inst)
+{
+    if (inst == SPK_INVALID_ID)
+    {
+        return 0u;
+    }
+    const DInstance *__restrict__ in = sc.instances + inst;
+    const DMaterial &m = sc.materials[__ldg(&in->material)];
+    uint32_t key = 1u;
+    key += __ldg(&in->kind) == 1u ? 0u : 1u;              // sphere / mesh
+    key += __ldg(&m.type) == 1u ? 2u : 0u;                // pbr / dielectric
+    bool tex = (__ldg(&m.base_color_tex) & __ldg(&m.metallic_roughness_tex) & __ldg(&m.normal_tex) &
+                __ldg(&m.emissive_tex)) != SPK_INVALID_ID; // any texture bound
+    key += tex ? 4u : 0u;
+    bool emissive = __ldg(&m.emissive[0]) != 0.f || __ldg(&m.emissive[1]) != 0.f || __ldg(&m.emissive[2]) != 0.f;
+    key += emissive ? 8u : 0u;
+    return key; // 0..16
+}
+
+// ---- shade: SamplePixel's loop body after Intersect (CPURenderer.cpp:259-369) for every traced slot
+__global__ void __launch_bounds__(kShadeThreads)
+    wf_shade_kernel(const DScene sc, const WfArgs a, WfState st, uint32_t cur, float4 *__restrict__ accum)
+{
+    __shared__ uint32_t s_bin[32];
+    __shared__ uint32_t s_sorted[kShadeThreads];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t k = blockIdx.x * kShadeThreads + tid;
+    const uint32_t n = st.ctrl->n_queue[cur];
+    if (blockIdx.x * kShadeThreads >= n)
+    {
+        return; // whole CTA beyond the queue
+    }
+    // -- CTA-local counting sort of this CTA's slots by material class
+    if (tid < 32)
+    {
+        s_bin[tid] = 0;
+    }
+    __syncthreads();
+    uint32_t my = kEmptySlot, key = 31u, pos = 0;
+    if (k < n)
+    {
+        my = st.queue[cur][k];
+        key = shade_class(sc, __float_as_uint(st.hit[my].w));
+    }
+    pos = atomicAdd(&s_bin[key], 1u);
+    __syncthreads();
+    if (tid < 32)
+    {
+        uint32_t c = s_bin[tid], incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1)
+        {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((int)lane >= d)
+            {
+                incl += t;
+            }
+        }
+        s_bin[tid] = incl - c; // exclusive start of the class
+    }
+    __syncthreads();
+    s_sorted[s_bin[key] + pos] = my;
+    __syncthreads();
+    const uint32_t slot = s_sorted[tid];
+
+    bool done = false, alive = slot != kEmptySlot;
+    V3 color = mk(0.f, 0.f, 0.f);
+    float valid = 1.f;
+    uint32_t pixel = 0;
+    if (alive)
+    {
+        const float4 ro = st.rays[2 * size_t(slot)], rd = st.rays[2 * size_t(slot) + 1];
+        const float4 h4 = st.hit[slot];
+        pixel = __float_as_uint(ro.w);
+        uint32_t bounce = __float_as_uint(rd.w);
+        V3 origin = mk(ro.x, ro.y, ro.z), dir = mk(rd.x, rd.y, rd.z);
+        const float4 t4 = st.thr[slot];
+        V3 throughput = mk(t4.x, t4.y, t4.z);
+        Hit hit;
+        hit.t = h4.x;
+        hit.u = h4.y;
+        hit.v = h4.z;
+        hit.inst = __float_as_uint(h4.w);
+        if (hit.inst == SPK_INVALID_ID)
+        {
+            if (sc.sky.has_sky)
+            {
+                color = cmul(sky_evaluate(sc, dir), throughput);
+            }
+            done = true;
+        }
+        else
+        {
+            hit.face = st.face[slot];
+            Surface sf;
+            get_intersection(sc, origin, dir, hit, sf);
+            V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
+            if (norm(emissive) > kEps)
+            {
+                color = cmul(emissive, throughput);
+                done = true;
+            }
+            else
+            {
+                const uint4 r4 = st.rng[slot];
+                Rng rng{r4.x, r4.y, r4.z, r4.w};
+                V3 next_dir;
+                V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
+                throughput = cmul(throughput, this_throughput);
+                if (sqnorm(throughput) < kEps)
+                {
+                    valid = -1.f;
+                    done = true;
+                }
+                else
+                {
+                    if (bounce >= 3)
+                    {
+                        float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
+                        p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
+                        if (rng_unit(rng) > p)
+                        {
+                            done = true;
+                        }
+                        else
+                        {
+                            throughput = throughput / p;
+                        }
+                    }
+                    if (!done)
+                    {
+                        bounce++;
+                        done = bounce >= a.max_bounce; // the bounce cap adds nothing (CPURenderer.cpp:256)
+                    }
+                    if (!done)
+                    {
+                        origin = sf.location + next_dir * kTolerance;
+                        st.rays[2 * size_t(slot)] = make_float4(origin.x, origin.y, origin.z, ro.w);
+                        st.rays[2 * size_t(slot) + 1] =
+                            make_float4(next_dir.x, next_dir.y, next_dir.z, __uint_as_float(bounce));
+                        st.rng[slot] = make_uint4(rng.s0, rng.s1, rng.s2, rng.s3);
+                        st.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.f);
+                    }
+                }
+            }
+        }
+    }
+    // -- finished paths: clamp and add (RenderPixel, CPURenderer.cpp:411-416); the slot goes to the regen list
+    if (alive && done)
+    {
+        float4 add = make_float4(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit),
+                                 fminf(color.z, a.output_limit), valid);
+        atomicAdd(accum + pixel, add); // one 16-byte vector reduction (sm_90+)
+    }
+    const uint32_t nxt = cur ^ 1u;
+    const unsigned m_cont = __ballot_sync(0xffffffffu, alive && !done);
+    const unsigned m_done = __ballot_sync(0xffffffffu, alive && done);
+    const unsigned lt = (1u << lane) - 1u;
+    uint32_t base_c = 0, base_d = 0;
+    if (lane == 0)
+    {
+        if (m_cont)
+        {
+            base_c = atomicAdd(&st.ctrl->n_queue[nxt], (uint32_t)__popc(m_cont));
+        }
+        if (m_done)
+        {
+            base_d = atomicAdd(&st.ctrl->n_regen, (uint32_t)__popc(m_done));
+        }
+    }
+    base_c = __shfl_sync(0xffffffffu, base_c, 0);
+    base_d = __shfl_sync(0xffffffffu, base_d, 0);
+    if (alive && !done)
+    {
+        st.queue[nxt][base_c + __popc(m_cont & lt)] = slot;
+    }
+    else if (alive)
+    {
+        st.regen[base_d + __popc(m_done & lt)] = slot;
+    }
+}
+} // namespace
+
+static uint32_t env_u32(const char *name, uint32_t dflt)
+{
+    const char *e = getenv(name);
+    return e && *e ? (uint32_t)strtoul(e, nullptr, 10) : dflt;
+}
+
+static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st)
+{
+    // one allocation, carved into 256-byte aligned arrays
+    auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t b_rays = al(size_t(slots) * 32), b_hit = al(size_t(slots) * 16), b_u32 = al(size_t(slots) * 4),
+                 b_rng = al(size_t(slots) * 16), b_thr = al(size_t(slots) * 16);
+    const size_t total = b_rays + b_hit + b_u32 * 4 + b_rng + b_thr + 256;
+    if (ctx->wf_slots != slots)
+    {
+        cudaFree(ctx->wf_block);
+        ctx->wf_block = nullptr;
+        ctx->wf_slots = 0;
+        SPK_CUDA_TRY(cudaMalloc(&ctx->wf_block, total));
+        ctx->wf_slots = slots;
+    }
+    char *p = static_cast<char *>(ctx->wf_block);
+    st.rays = reinterpret_cast<float4 *>(p);
+    p += b_rays;
+    st.hit = reinterpret_cast<float4 *>(p);
+    p += b_hit;
+    st.rng = reinterpret_cast<uint4 *>(p);
+    p += b_rng;
+    st.thr = reinterpret_cast<float4 *>(p);
+    p += b_thr;
+    st.face = reinterpret_cast<uint32_t *>(p);
+    p += b_u32;
+    st.queue[0] = reinterpret_cast<uint32_t *>(p);
+    p += b_u32;
+    st.queue[1] = reinterpret_cast<uint32_t *>(p);
+    p += b_u32;
+    st.regen = reinterpret_cast<uint32_t *>(p);
+    p += b_u32;
+    st.ctrl = reinterpret_cast<WfCtrl *>(p);
+    st.slots = slots;
+    return SPK_OK;
+}
+
+template <bool CULL, bool COUNT>
+static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t sample_count)
+{
+    auto extend = wf_extend_kernel<CULL, COUNT, 16>;
+    static int blocks_per_sm = 0, sms = 0;
+    if (blocks_per_sm == 0)
+    {
+        SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, extend, kExtendWarps * 32, 0));
+        SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+        blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
+    }
+    const unsigned long long total = (unsigned long long)a.width * a.height * sample_count;
+    const uint32_t slots = st.slots;
+    const unsigned slot_blocks = (slots + kShadeThreads - 1) / kShadeThreads;
+    unsigned extend_blocks = (slots + kExtendWarps * 32 - 1) / (kExtendWarps * 32);
+    const unsigned resident = unsigned(blocks_per_sm) * unsigned(sms); // one wave of persistent CTAs
+    extend_blocks = extend_blocks < resident ? extend_blocks : resident;
+    cudaStream_t s = ctx->stream;
+    wf_init_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(st, total);
+    ctx->stats.kernel_launches++;
+    // every iteration traces one segment of every live slot; the host looks at the control block once per chunk
+    const uint32_t chunk = env_u32("SPK_WF_CHUNK", 32);
+    uint32_t cur = 0;
+    WfCtrl h{};
+    for (;;)
+    {
+        for (uint32_t it = 0; it < chunk; it++)
+        {
+            wf_shade_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur, ctx->d_accum);
+            wf_regen_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->camera, a, st, cur ^ 1u);
+            wf_advance_kernel<<<1, 1, 0, s>>>(st, cur, ctx->d_counters);
+            extend<<<extend_blocks, kExtendWarps * 32, 0, s>>>(ctx->scene, st, cur ^ 1u, ctx->d_counters);
+            ctx->stats.kernel_launches += 4;
+            cur ^= 1u;
+        }
+        SPK_CUDA_TRY(cudaGetLastError());
+        SPK_CUDA_TRY(cudaMemcpyAsync(&h, st.ctrl, sizeof(h), cudaMemcpyDeviceToHost, s));
+        SPK_CUDA_TRY(cudaStreamSynchronize(s));
+        if (h.work_next >= h.work_total && h.n_queue[cur] == 0)
+        {
+            break;
+        }
+    }
+    return SPK_OK;
+}
+
+int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *p)
+{
+    if (p->accum_mode != SPK_ACCUM_SUM)
+    {
+        set_error("spk_cuda_render: the wavefront tracer adds samples in arbitrary order: SPK_ACCUM_SUM only");
+        return SPK_ERR_UNSUPPORTED;
+    }
+    if ((p->flags >> 8) & 3u)
+    {
+        set_error("spk_cuda_render: parity probes (debug flags) are a megakernel feature");
+        return SPK_ERR_UNSUPPORTED;
+    }
+    WfArgs a;
+    a.width = ctx->width;
+    a.height = ctx->height;
+    a.first_sample = p->first_sample;
+    a.sample_stride = p->sample_stride ? p->sample_stride : 1u;
+    a.max_bounce = p->max_bounce;
+    a.output_limit = p->output_limit;
+    const unsigned long long total = (unsigned long long)a.width * a.height * p->sample_count;
+    uint32_t slots = env_u32("SPK_WF_SLOTS", 1u << 20);
+    if (slots > total)
+    {
+        slots = uint32_t(total);
+    }
+    slots = (slots + 255u) & ~255u;
+    WfState st;
+    int rc = wf_reserve(ctx, slots, st);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
+    if (exact && count)
+        return wf_run<false, true>(ctx, a, st, p->sample_count);
+    if (exact)
+        return wf_run<false, false>(ctx, a, st, p->sample_count);
+    if (count)
+        return wf_run<true, true>(ctx, a, st, p->sample_count);
+    return wf_run<true, false>(ctx, a, st, p->sample_count);
+}
+} // namespace spk

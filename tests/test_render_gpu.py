@@ -124,3 +124,32 @@ def test_running_average_and_resolve_formats(oracle):
     srgb = ctx.resolve(A.RESOLVE_TONEMAP_SRGB8)
     assert srgb.shape == (h, w, 4) and srgb[..., 3].min() == 255 and srgb[..., :3].max() > 100
     ctx.close()
+
+
+@pytest.mark.parametrize("name,bounce,spp", [("testscene", 8, 8), ("city", 8, 4), ("room", 32, 4)])
+def test_wavefront_equals_megakernel(name, bounce, spp, oracle, monkeypatch):
+    """SPK_FLAG_WAVEFRONT: the same samples through the queue tracer; only the order of the per-pixel sum differs"""
+    w, h = 128, 72
+    sb, desc, cam = build(name, w, h)
+    ctx = CudaContext(w, h)
+    ctx.upload_scene(desc)
+    ctx.set_camera(cam)
+    ctx.render(first_sample=2, sample_count=spp, max_bounce=bounce)
+    mega = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    st_m = ctx.stats()
+    for slots in ("1024", "1048576"):  # pool smaller than one sample of the image / larger than the whole job
+        monkeypatch.setenv("SPK_WF_SLOTS", slots)
+        ctx.reset_accumulation()
+        ctx.reset_stats()
+        ctx.render(first_sample=2, sample_count=spp, max_bounce=bounce, flags=A.FLAG_WAVEFRONT)
+        wave = ctx.resolve(A.RESOLVE_LINEAR_F32)
+        st_w = ctx.stats()
+        assert np.allclose(wave, mega, rtol=2e-6, atol=1e-6), np.abs(wave - mega).max()
+        assert st_w["paths"] == w * h * spp
+        assert st_w["rays"] == st_m["rays"]  # the same paths, segment for segment
+    ref, _ = oracle.render(desc, cam, w, h, first_sample=2, sample_count=spp, max_bounce=bounce)
+    m = image_metrics(wave, ref / spp)
+    assert m["mean_rel"] <= MEAN_REL_TOL, m
+    with pytest.raises(A.SpkError):
+        ctx.render(0, 1, accum_mode=A.ACCUM_RUNNING_AVERAGE, flags=A.FLAG_WAVEFRONT)
+    ctx.close()
