@@ -27,6 +27,33 @@ sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT, SPP, BOUNCE = 1920, 1080, 256, 8
 WORKLOAD = "TestScene-procedural, cuda pipeline, 1920x1080, 256 spp, max depth 8 (BASELINE.json configs[1])"
+SCENE = "testscene"
+# --workload: the headline (c2) is what the driver runs; c4 / c5 are the scaling configs of BASELINE.json (configs[3],
+# configs[4]); --spp bounds them (stated in config.workload) so a run stays within minutes
+WORKLOADS = {
+    "c2": ("testscene", 1920, 1080, 256, 8,
+           "TestScene-procedural, cuda pipeline, 1920x1080, 256 spp, max depth 8 (BASELINE.json configs[1])"),
+    "c4": ("city", 3840, 2160, 1024, 8,
+           "city-10M (16 meshes x 62,500 tris, 160 instances = 10.0M instanced triangles), 3840x2160, 1024 spp, "
+           "max depth 8, diffuse+glossy (BASELINE.json configs[3])"),
+    "c5": ("room", 1920, 1080, 256, 32,
+           "closed room, textured materials, emissive panel, 1920x1080, 256 spp, max depth 32 + Russian roulette "
+           "(BASELINE.json configs[4])"),
+}
+
+
+def select_workload(args):
+    global WIDTH, HEIGHT, SPP, BOUNCE, WORKLOAD, SCENE
+    SCENE, WIDTH, HEIGHT, SPP, BOUNCE, WORKLOAD = WORKLOADS[args.workload]
+    if args.spp:
+        WORKLOAD += f" -- bounded to {args.spp} spp of {SPP} for this run"
+        SPP = args.spp
+
+
+def build_scene():
+    from sparkle_b200 import scenes
+    sb, camkw = getattr(scenes, SCENE)()
+    return sb, camkw
 
 
 def peaks():
@@ -115,12 +142,11 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from sparkle_b200 import scenes
     from sparkle_b200.scene import orbit_camera
-    sb, camkw = scenes.testscene()
+    sb, camkw = build_scene()
     desc = sb.finalize()
     cam = orbit_camera(WIDTH, HEIGHT, **camkw)
-    spp_step = 16  # ~1.7 s of CPU work per step on 15 workers
+    spp_step = 16 if SCENE == "testscene" else 2  # ~1.7 s of CPU work per step on 15 workers (testscene)
     for w in range(args.warmup):
         cpu_render_rate(desc, cam, spp_step, first_sample=w * spp_step)
     t0 = time.perf_counter()
@@ -154,7 +180,7 @@ def run_cuda(args):
     import torch
     import torch.distributed as dist
     from sparkle_b200 import _abi as A
-    from sparkle_b200 import multi_gpu, scenes
+    from sparkle_b200 import multi_gpu
     from sparkle_b200.device import CudaContext
     from sparkle_b200.scene import orbit_camera
 
@@ -168,7 +194,7 @@ def run_cuda(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     first_sample, spp_rank, stride = multi_gpu.sample_slice(SPP, rank, world)
 
-    sb, camkw = scenes.testscene()
+    sb, camkw = build_scene()
     desc = sb.finalize()
     cam = orbit_camera(WIDTH, HEIGHT, **camkw)
     ctx = CudaContext(WIDTH, HEIGHT, device=local)
@@ -185,9 +211,17 @@ def run_cuda(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # megakernel or wavefront: measured on this scene (spk_cuda_choose_tracer), the same choice SPK_FLAG_AUTO_TRACER makes
+    if args.tracer == "auto":
+        use_wavefront, choose_ms = ctx.choose_tracer(BOUNCE)
+    else:
+        use_wavefront, choose_ms = args.tracer == "wavefront", None
+    tracer_flag = A.FLAG_WAVEFRONT if use_wavefront else 0
+
     def device_step():
         ctx.reset_accumulation()
-        ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE)
+        ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE,
+                   flags=tracer_flag)
         multi_gpu.reduce_accumulator(accum_t, world, dst=0)  # ONE NCCL reduce over NVLink
 
     def timed(step_fn, steps, warmup):
@@ -212,7 +246,8 @@ def run_cuda(args):
     ctx.reset_stats()
     ctx.reset_accumulation()
     cspp = max(1, spp_rank // 16)
-    ctx.render(first_sample=first_sample, sample_count=cspp, sample_stride=stride, max_bounce=BOUNCE, flags=A.FLAG_COUNTERS)
+    ctx.render(first_sample=first_sample, sample_count=cspp, sample_stride=stride, max_bounce=BOUNCE,
+               flags=A.FLAG_COUNTERS | tracer_flag)
     cst = ctx.stats()
     ctx.reset_stats()
 
@@ -221,7 +256,8 @@ def run_cuda(args):
         sampler.start()
     launches0 = ctx.stats()["kernel_launches"]
     ms_total = timed(device_step, args.steps, args.warmup)
-    launches = ctx.stats()["kernel_launches"] - launches0 - args.warmup
+    # every step launches the same kernels: the timed share of (warm-up + timed) launches
+    launches = (ctx.stats()["kernel_launches"] - launches0) * args.steps // (args.steps + args.warmup)
     st = ctx.stats()
     clocks = sampler.stop() if rank == 0 else None
 
@@ -233,7 +269,8 @@ def run_cuda(args):
         ctx.upload_scene(desc)
         ctx.set_camera(cam)
         ctx.reset_accumulation()
-        ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE)
+        ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE,
+                   flags=A.FLAG_AUTO_TRACER if args.tracer == "auto" else tracer_flag)
         multi_gpu.reduce_accumulator(accum_t, world, dst=0)
         if rank == 0:
             ctx.resolve(A.RESOLVE_TONEMAP_F16, total_samples=SPP)
@@ -264,19 +301,22 @@ def run_cuda(args):
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "parallelism": f"spp-split x{world}", "l2": "flushed between steps (256 MB fill)",
+                   "tracer": "wavefront" if use_wavefront else "megakernel",
+                   "tracer_choice_ms_4spp": {"megakernel": choose_ms[0], "wavefront": choose_ms[1]} if choose_ms else None,
                    "mrays_per_s": rays_total / (kernel_ms * 1e-3) / 1e6, "rays_per_path": rays_launch / paths_launch},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / e2e_steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "render_phased_kernel<CULL=true, 8 warps x 3 CTAs/SM>",
+                     "traffic": None, "peak_source": peak_src, "kernel": ("wf_extend_kernel<CULL=true> (+ wf_shade/regen/advance; achieved is over the whole step)"
+                                if use_wavefront else "render_phased_kernel<CULL=true, 8 warps x 3 CTAs/SM>"),
                      "alg_bytes_per_ray": alg_bytes / max(1.0, rays_launch),
                      "node_visits_per_ray": cst["node_visits"] / max(1, cst["rays"]),
                      "tri_tests_per_ray": cst["tri_tests"] / max(1, cst["rays"])},
     }
     if not args.no_cpu_baseline and world == 1:
-        cpu_spp = 128  # ~13 s on 15 workers
+        cpu_spp = 128 if SCENE == "testscene" else 4  # ~13 s on 15 workers (testscene)
         v, dt, cores, kind = cpu_render_rate(desc, cam, cpu_spp)
         line["cpu_baseline"] = {"value": v, "unit": "Mpaths/s", "cores": cores,
                                 "kind": "reference" if kind == "reference" else "port",
@@ -293,7 +333,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="bound the workload's spp (stated in config.workload)")
+    ap.add_argument("--tracer", default="auto", choices=["auto", "megakernel", "wavefront"])
     args = ap.parse_args()
+    select_workload(args)
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":
         run_reference(args)

@@ -172,8 +172,10 @@ enum {
     SPK_FLAG_EXACT_TRAVERSAL = 1u, /* never shorten tmax while traversing (reference behaviour) */
     SPK_FLAG_COUNTERS = 2u,        /* instrumented kernel: fill node/triangle counters in SpkStats */
     SPK_FLAG_WAVEFRONT = 4u,       /* wavefront (queue) tracer instead of the persistent megakernel */
-    SPK_FLAG_THREAD_PER_RAY = 8u   /* ray batches: plain one-thread-per-ray kernel instead of the persistent warp-voting one
+    SPK_FLAG_THREAD_PER_RAY = 8u,  /* ray batches: plain one-thread-per-ray kernel instead of the persistent warp-voting one
                                       (kept for A/B measurement; same results) */
+    SPK_FLAG_AUTO_TRACER = 16u     /* megakernel or wavefront, whichever spk_cuda_choose_tracer measured faster on the
+                                      current scene (measured on first use if not yet); SPK_ACCUM_SUM only, else megakernel */
 };
 
 typedef struct SpkRenderParams {
@@ -250,6 +252,11 @@ int spk_cuda_set_camera(SpkContext *ctx, const SpkCamera *camera);
 int spk_cuda_reset_accumulation(SpkContext *ctx);
 /* CPURenderer::BasePass + temporal accumulate (CPURenderer.cpp:419-450, 530-544) for sample_count samples. */
 int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params);
+/* Times a few samples per pixel of the current scene and camera with the megakernel and with the wavefront tracer
+ * (CUDA events) and remembers the faster one for SPK_FLAG_AUTO_TRACER until the next spk_cuda_upload_scene. The
+ * accumulator must be empty (it is used as scratch and cleared again). *wavefront_out: 0 megakernel, 1 wavefront;
+ * ms_out[2]: the two times (may be NULL). */
+int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavefront_out, float *ms_out);
 /* ToneMappingPass + readback (CPURenderer.cpp:554-576; Renderer.cpp:108-180). `total_samples` is the
  * number of samples summed in the accumulator (all ranks, after the reduce) for SPK_ACCUM_SUM. */
 int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, void *host_out, size_t host_bytes);

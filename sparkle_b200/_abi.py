@@ -14,7 +14,7 @@ PRIM_MESH, PRIM_SPHERE = 0, 1
 MAT_PBR, MAT_DIELECTRIC = 0, 1
 FMT_RGBA8_UNORM, FMT_RGBA8_SRGB, FMT_RGBA16F, FMT_RGBA32F = 0, 1, 2, 3
 ACCUM_SUM, ACCUM_RUNNING_AVERAGE = 0, 1
-FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY = 1, 2, 4, 8
+FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY, FLAG_AUTO_TRACER = 1, 2, 4, 8, 16
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
 
 u32, i32, f32, u64 = C.c_uint32, C.c_int32, C.c_float, C.c_uint64
@@ -104,6 +104,7 @@ CUDA_SYMBOLS = {
     "spk_cuda_reset_accumulation": (C.c_int, [CtxP]),
     "spk_cuda_render": (C.c_int, [CtxP, C.POINTER(RenderParams)]),
     "spk_cuda_resolve": (C.c_int, [CtxP, u32, u32, C.c_void_p, C.c_size_t]),
+    "spk_cuda_choose_tracer": (C.c_int, [CtxP, u32, C.POINTER(u32), C.POINTER(C.c_float)]),
     "spk_cuda_accum_device_ptr": (C.c_int, [CtxP, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "spk_cuda_accum_sample_count": (C.c_int, [CtxP, u32p]),
     "spk_cuda_trace_closest": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),

@@ -510,6 +510,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     ctx->scene.cull_extent = s->world_extent > 0.f ? s->world_extent : 1.f;
     ctx->scene.sky = sky;
     ctx->has_scene = true;
+    ctx->tracer_choice = -1; // measured again for the new scene (spk_cuda_choose_tracer)
     return SPK_OK;
 }
 

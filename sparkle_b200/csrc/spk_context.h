@@ -48,6 +48,7 @@ struct SpkContext
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
     void *wf_block = nullptr;
     uint32_t wf_slots = 0;
+    int tracer_choice = -1; // -1 not measured for this scene, 0 megakernel, 1 wavefront (spk_cuda_choose_tracer)
 };
 
 namespace spk

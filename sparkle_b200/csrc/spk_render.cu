@@ -516,8 +516,20 @@ int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params)
     }
     SPK_CUDA_TRY(cudaSetDevice(ctx->device));
     SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+    if ((params->flags & SPK_FLAG_AUTO_TRACER) && ctx->tracer_choice < 0 && ctx->accum_samples == 0 &&
+        params->accum_mode == SPK_ACCUM_SUM && params->max_bounce != 0u)
+    {
+        uint32_t w = 0;
+        int rc0 = spk_cuda_choose_tracer(ctx, params->max_bounce, &w, nullptr);
+        if (rc0 != SPK_OK)
+        {
+            return rc0;
+        }
+    }
+    const bool automatic = (params->flags & SPK_FLAG_AUTO_TRACER) && ctx->tracer_choice == 1 &&
+                           params->accum_mode == SPK_ACCUM_SUM && ((params->flags >> 8) & 3u) == 0u;
     // a zero-iteration bounce loop has nothing to queue: the megakernel handles it
-    const bool wavefront = (params->flags & SPK_FLAG_WAVEFRONT) && params->max_bounce != 0u;
+    const bool wavefront = ((params->flags & SPK_FLAG_WAVEFRONT) || automatic) && params->max_bounce != 0u;
     int rc = wavefront ? launch_render_wavefront(ctx, params) : launch_render(ctx, params);
     if (rc != SPK_OK)
     {
@@ -526,6 +538,78 @@ int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params)
     SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->accum_mode = params->accum_mode;
     ctx->accum_samples += params->sample_count;
+    return SPK_OK;
+}
+
+int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavefront_out, float *ms_out)
+{
+    if (!ctx || !wavefront_out || max_bounce == 0u)
+    {
+        set_error("spk_cuda_choose_tracer: null argument or max_bounce 0");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (!ctx->has_scene || !ctx->has_camera)
+    {
+        set_error("spk_cuda_choose_tracer: needs a scene and a camera");
+        return SPK_ERR_NO_SCENE;
+    }
+    if (ctx->accum_samples != 0)
+    {
+        set_error("spk_cuda_choose_tracer: the accumulator is in use (spk_cuda_reset_accumulation first)");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    unsigned long long saved[8];
+    SPK_CUDA_TRY(cudaMemcpyAsync(saved, ctx->d_counters, sizeof(saved), cudaMemcpyDeviceToHost, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    SpkRenderParams p{};
+    p.first_sample = 0;
+    p.sample_count = 4;
+    p.sample_stride = 1;
+    p.max_bounce = max_bounce;
+    p.output_limit = 6.f;
+    p.accum_mode = SPK_ACCUM_SUM;
+    cudaEvent_t e0, e1;
+    SPK_CUDA_TRY(cudaEventCreate(&e0));
+    SPK_CUDA_TRY(cudaEventCreate(&e1));
+    float ms[2] = {0.f, 0.f};
+    int rc = SPK_OK;
+    for (int which = 0; which < 2 && rc == SPK_OK; which++)
+    {
+        float best = 3.4e38f;
+        for (int rep = 0; rep < 2 && rc == SPK_OK; rep++) // first repetition warms caches and lazy module loading
+        {
+            cudaEventRecord(e0, ctx->stream);
+            rc = which ? launch_render_wavefront(ctx, &p) : launch_render(ctx, &p);
+            cudaEventRecord(e1, ctx->stream);
+            if (cudaEventSynchronize(e1) != cudaSuccess)
+            {
+                rc = cuda_fail(cudaGetLastError(), "spk_cuda_choose_tracer");
+                break;
+            }
+            float t = 0.f;
+            cudaEventElapsedTime(&t, e0, e1);
+            best = t < best ? t : best;
+        }
+        ms[which] = best;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    // scratch use only: the accumulator and the counters go back to what they were
+    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_accum, 0, size_t(ctx->width) * ctx->height * sizeof(float4), ctx->stream));
+    SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_counters, saved, sizeof(saved), cudaMemcpyHostToDevice, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    ctx->tracer_choice = ms[1] < ms[0] ? 1 : 0;
+    *wavefront_out = (uint32_t)ctx->tracer_choice;
+    if (ms_out)
+    {
+        ms_out[0] = ms[0];
+        ms_out[1] = ms[1];
+    }
     return SPK_OK;
 }
 

@@ -67,7 +67,9 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    uint32_t stack[kWarpStack];
+    __shared__ uint32_t s_stack[kPersistWarps * kSmemStack * 32];
+    LaneStack stack;
+    stack.sm = s_stack + (threadIdx.x >> 5) * (kSmemStack * 32) + (threadIdx.x & 31u);
     LaneState s;
     TraceCounters cnt{0, 0, 0, 0};
     unsigned long long ray_id = ~0ull;

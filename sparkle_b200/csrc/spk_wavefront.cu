@@ -155,7 +155,9 @@ __global__ void __launch_bounds__(kExtendWarps * 32)
     const uint32_t *__restrict__ queue = st.queue[q];
     const float4 *__restrict__ rays = st.rays;
     uint32_t *next_ray = &st.ctrl->next_ray;
-    uint32_t stack[kWarpStack];
+    __shared__ uint32_t s_stack[kExtendWarps * kSmemStack * 32];
+    LaneStack stack;
+    stack.sm = s_stack + (threadIdx.x >> 5) * (kSmemStack * 32) + (threadIdx.x & 31u);
     LaneState s;
     TraceCounters cnt{0, 0, 0, 0};
     uint32_t slot = kEmptySlot;
@@ -486,10 +488,13 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t 
     wf_init_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(st, total);
     ctx->stats.kernel_launches++;
     // every iteration traces one segment of every live slot; the host looks at the control block once per chunk
-    const uint32_t chunk = env_u32("SPK_WF_CHUNK", 32);
+    // first look after the fewest iterations the job can take (one segment per path), then every few iterations
+    unsigned long long least = (total + slots - 1) / slots + a.max_bounce;
+    uint32_t chunk = uint32_t(least < 4096ull ? least : 4096ull);
+    const uint32_t chunk_next = env_u32("SPK_WF_CHUNK", 8);
     uint32_t cur = 0;
     WfCtrl h{};
-    for (;;)
+    for (;; chunk = chunk_next)
     {
         for (uint32_t it = 0; it < chunk; it++)
         {

@@ -82,6 +82,12 @@ class CudaContext:
     def trace_closest_device(self, d_rays, n, d_hits, flags=0):
         A.check(self.lib.spk_cuda_trace_closest_device(self.handle, C.c_void_p(d_rays), n, C.c_void_p(d_hits), flags))
 
+    def choose_tracer(self, max_bounce=8):
+        """measure megakernel vs wavefront on the current scene; returns (wavefront?, (ms_mega, ms_wave))"""
+        w, ms = C.c_uint32(0), (C.c_float * 2)()
+        A.check(self.lib.spk_cuda_choose_tracer(self.handle, max_bounce, C.byref(w), ms))
+        return bool(w.value), (ms[0], ms[1])
+
     def stats(self):
         s = A.Stats()
         A.check(self.lib.spk_cuda_get_stats(self.handle, C.byref(s)))
