@@ -270,7 +270,7 @@ def run_cuda(args):
         ctx.set_camera(cam)
         ctx.reset_accumulation()
         ctx.render(first_sample=first_sample, sample_count=spp_rank, sample_stride=stride, max_bounce=BOUNCE,
-                   flags=A.FLAG_AUTO_TRACER if args.tracer == "auto" else tracer_flag)
+                   flags=tracer_flag)  # the tracer was chosen once for this scene, as CudaRenderer does at init
         multi_gpu.reduce_accumulator(accum_t, world, dst=0)
         if rank == 0:
             ctx.resolve(A.RESOLVE_TONEMAP_F16, total_samples=SPP)

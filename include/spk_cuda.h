@@ -174,6 +174,10 @@ enum {
     SPK_FLAG_WAVEFRONT = 4u,       /* wavefront (queue) tracer instead of the persistent megakernel */
     SPK_FLAG_THREAD_PER_RAY = 8u,  /* ray batches: plain one-thread-per-ray kernel instead of the persistent warp-voting one
                                       (kept for A/B measurement; same results) */
+    SPK_FLAG_SPATIAL_DENOISE = 32u, /* RenderConfig::spatial_denoise (CPURenderer.cpp:452-526): every sample is rendered
+                                      into a g-buffer (colour + valid flag, first-hit normal), invalid pixels take the
+                                      colour of a valid non-sky 8-neighbour with normal similarity >= 0.99, then the
+                                      sample is accumulated. One sample per pixel per pass like the reference; megakernel */
     SPK_FLAG_AUTO_TRACER = 16u     /* megakernel or wavefront, whichever spk_cuda_choose_tracer measured faster on the
                                       current scene (measured on first use if not yet); SPK_ACCUM_SUM only, else megakernel */
 };

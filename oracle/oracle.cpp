@@ -1290,6 +1290,13 @@ int orc_render(const SpkSceneDesc *scene, const SpkCamera *camera, uint32_t widt
     uint32_t nt = std::max(1u, threads);
     std::vector<Counters> per_thread(nt);
     std::vector<float> frame(size_t(width) * height * 4); // gbuffer_.color of one sample
+    const bool spatial = params->flags & SPK_FLAG_SPATIAL_DENOISE;
+    if (spatial && params->accum_mode != SPK_ACCUM_RUNNING_AVERAGE)
+    {
+        return SPK_ERR_UNSUPPORTED; // the reference's DenoisePass is the running average
+    }
+    std::vector<float> normals(spatial ? size_t(width) * height * 3 : 0); // gbuffer_.world_normal
+    std::vector<float> filled;                                             // ping_pong_buffer_
     uint32_t stride = std::max(1u, params->sample_stride);
     for (uint32_t s = 0; s < params->sample_count; s++)
     {
@@ -1304,8 +1311,61 @@ int orc_render(const SpkSceneDesc *scene, const SpkCamera *camera, uint32_t widt
                 px[1] = ps.color.y;
                 px[2] = ps.color.z;
                 px[3] = ps.valid;
+                if (spatial)
+                {
+                    float *pn = normals.data() + (size_t(j) * width + i) * 3;
+                    pn[0] = ps.world_normal.x;
+                    pn[1] = ps.world_normal.y;
+                    pn[2] = ps.world_normal.z;
+                }
             }
         });
+        if (spatial)
+        {
+            // DenoisePass, spatial part (CPURenderer.cpp:511-526) + SpatialDenoisePixel (:452-504), rows in order (one
+            // worker): each valid non-sky pixel gives its colour to the FIRST of its 8 neighbours, in the reference's
+            // direction order, that is invalid and has normal similarity >= 0.99; later writers overwrite earlier ones
+            static const int dirs[8][2] = {{1, 0}, {0, 1}, {-1, 0}, {0, -1}, {-1, -1}, {1, -1}, {-1, 1}, {1, 1}};
+            filled = frame;
+            for (uint32_t j = 0; j < height; j++)
+            {
+                for (uint32_t i = 0; i < width; i++)
+                {
+                    const float *c = frame.data() + (size_t(j) * width + i) * 4;
+                    const float *n = normals.data() + (size_t(j) * width + i) * 3;
+                    if (!(c[3] > 0.f) || (n[0] == 0.f && n[1] == 0.f && n[2] == 0.f))
+                    {
+                        continue;
+                    }
+                    for (int k = 0; k < 8; k++)
+                    {
+                        int si = int(i) + dirs[k][0], sj = int(j) + dirs[k][1];
+                        if (si < 0 || si >= int(width) || sj < 0 || sj >= int(height))
+                        {
+                            continue;
+                        }
+                        const float *nc = frame.data() + (size_t(sj) * width + si) * 4;
+                        const float *nn = normals.data() + (size_t(sj) * width + si) * 3;
+                        if (nc[3] > 0.f)
+                        {
+                            continue;
+                        }
+                        float similarity = (nn[0] * n[0] + nn[1] * n[1]) + nn[2] * n[2];
+                        if (similarity < 0.99f)
+                        {
+                            continue;
+                        }
+                        float *o = filled.data() + (size_t(sj) * width + si) * 4;
+                        o[0] = c[0];
+                        o[1] = c[1];
+                        o[2] = c[2];
+                        o[3] = 1.f;
+                        break;
+                    }
+                }
+            }
+            frame.swap(filled);
+        }
         if (params->accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
         {
             // DenoisePass, temporal part (CPURenderer.cpp:526-544): acc = Lerp(new, acc, N / (N + spp)), spp = 1

@@ -711,9 +711,16 @@ int orc_render(const SpkSceneDesc *scene, const SpkCamera *camera, uint32_t widt
 
     RenderConfig cfg;
     FillRenderConfig(cfg, width, height, params->max_bounce);
+    const bool spatial = params->flags & SPK_FLAG_SPATIAL_DENOISE;
+    if (spatial && params->accum_mode != SPK_ACCUM_RUNNING_AVERAGE)
+    {
+        return SPK_ERR_UNSUPPORTED; // the reference's DenoisePass is the running average
+    }
+    cfg.spatial_denoise = spatial; // RenderPixel stores first-hit normals, DenoisePass fills invalid neighbours
     CPURenderer renderer(cfg, nullptr, rs->scene.get());
     renderer.camera_ = rs->camera.get();
     renderer.gbuffer_.Resize(width, height);
+    renderer.ping_pong_buffer_.assign(height, std::vector<Vector4>(width, Vector4::Zero()));
     renderer.frame_buffer_.assign(height, std::vector<Vector4>(width, Vector4::Zero()));
     renderer.sub_pixel_count_ = 1;
     renderer.actual_sample_per_pixel_ = 1;

@@ -15,6 +15,7 @@ MAT_PBR, MAT_DIELECTRIC = 0, 1
 FMT_RGBA8_UNORM, FMT_RGBA8_SRGB, FMT_RGBA16F, FMT_RGBA32F = 0, 1, 2, 3
 ACCUM_SUM, ACCUM_RUNNING_AVERAGE = 0, 1
 FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY, FLAG_AUTO_TRACER = 1, 2, 4, 8, 16
+FLAG_SPATIAL_DENOISE = 32
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
 
 u32, i32, f32, u64 = C.c_uint32, C.c_int32, C.c_float, C.c_uint64

@@ -277,6 +277,7 @@ int spk_cuda_destroy(SpkContext *ctx)
     cudaFree(ctx->d_hits);
     cudaFree(ctx->d_resolve);
     cudaFree(ctx->wf_block);
+    cudaFree(ctx->d_gbuf);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream)

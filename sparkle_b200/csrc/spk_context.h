@@ -30,6 +30,7 @@ struct SpkContext
     spk::DCamera camera{};
 
     float4 *d_accum = nullptr; // W*H float4
+    float4 *d_gbuf = nullptr;  // 2 x W*H float4 (colour + valid, first-hit normal), allocated on first denoised render
     uint32_t accum_samples = 0;
     uint32_t accum_mode = 0; // SpkAccumMode of the samples in d_accum
 
@@ -67,5 +68,6 @@ int cuda_fail(cudaError_t e, const char *what);
 int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags);
 int launch_render(SpkContext *ctx, const SpkRenderParams *params);
 int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *params);
+int launch_denoise_accumulate(SpkContext *ctx, uint32_t spatial, uint32_t accum_mode, uint32_t cumulated);
 int launch_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, uint32_t accum_mode, void *d_out);
 } // namespace spk

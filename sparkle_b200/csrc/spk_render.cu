@@ -37,7 +37,9 @@ struct RenderArgs
     uint32_t cumulated; // samples already in the accumulator (running-average mode)
 };
 
-template <bool CULL, bool COUNT>
+// GBUF: one sample per pixel into a g-buffer instead of the accumulator (RenderPixel with spatial_denoise,
+// CPURenderer.cpp:411-416): gbuf[p] = (min(colour, limit), valid), gbuf[W*H + p] = (first-hit normal, 0)
+template <bool CULL, bool COUNT, bool GBUF = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
     render_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
                   unsigned long long *__restrict__ counters)
@@ -58,7 +60,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
         const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
         const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
         const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
-        float4 acc = accum[size_t(j) * a.width + i];
+        float4 acc = GBUF ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(j) * a.width + i];
+        V3 first_normal = mk(0.f, 0.f, 0.f);
         uint32_t stack[64];
         for (uint32_t s = 0; s < a.sample_count; s++)
         {
@@ -93,6 +96,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
                 }
                 Surface sf;
                 get_intersection(sc, origin, dir, hit, sf);
+                if (GBUF && bounce == 0)
+                {
+                    first_normal = sf.normal; // SampleResult::world_normal (CPURenderer.cpp:280-283)
+                }
                 if (a.debug)
                 {
                     // parity probes (tests only): first-hit normal / tangent / (u, v, t)
@@ -127,7 +134,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
                 dir = next_dir;
             }
             color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
-            if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
+            if (GBUF)
+            {
+                acc = make_float4(color.x, color.y, color.z, valid);
+            }
+            else if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
             {
                 uint32_t n = a.cumulated + s;
                 float ma = (float)n / (float)(n + 1u);
@@ -140,6 +151,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
             }
         }
         accum[size_t(j) * a.width + i] = acc;
+        if (GBUF)
+        {
+            accum[size_t(a.width) * a.height + size_t(j) * a.width + i] =
+                make_float4(first_normal.x, first_normal.y, first_normal.z, 0.f);
+        }
     }
     uint32_t total = __reduce_add_sync(0xffffffffu, rays);
     uint32_t pixels = __popc(__ballot_sync(0xffffffffu, i < a.width && j < a.height));
@@ -428,7 +444,7 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
         const char *e = getenv("SPK_RENDER_PHASED");
         return e ? atoi(e) : 831; // default: 8 warps per CTA, 3 CTAs per SM, both barriers (measured best)
     }();
-    if (phased != 0)
+    if (phased != 0 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE))
     {
         // SPK_RENDER_PHASED = warps*100 + min_blocks*10 + second_barrier selects a measured variant; 0 = render_kernel
 #define SPK_PHASED_CASE(W, B, S2)                                                                                      \
@@ -462,6 +478,32 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
         return SPK_OK;
     }
     dim3 grid{(tiles + kWarpsPerBlock - 1) / kWarpsPerBlock}, block{kWarpsPerBlock * 32};
+    if (p->flags & SPK_FLAG_SPATIAL_DENOISE)
+    {
+        // the reference's frame: BasePass (one sample into the g-buffer), then DenoisePass (fill + accumulate)
+        if (!ctx->d_gbuf)
+        {
+            SPK_CUDA_TRY(cudaMalloc(&ctx->d_gbuf, size_t(a.width) * a.height * 2 * sizeof(float4)));
+        }
+        const uint32_t first = a.first_sample, count = a.sample_count;
+        a.sample_count = 1;
+        for (uint32_t s = 0; s < count; s++)
+        {
+            a.first_sample = first + s * a.sample_stride;
+            if (exact)
+                render_kernel<false, false, true><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_gbuf, ctx->d_counters);
+            else
+                render_kernel<true, false, true><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_gbuf, ctx->d_counters);
+            SPK_CUDA_TRY(cudaGetLastError());
+            ctx->stats.kernel_launches++;
+            int rc = launch_denoise_accumulate(ctx, 1u, a.accum_mode, ctx->accum_samples + s);
+            if (rc != SPK_OK)
+            {
+                return rc;
+            }
+        }
+        return SPK_OK;
+    }
 #define SPK_LAUNCH_RENDER(C, N)                                                                                        \
     render_kernel<C, N><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters)
     if (exact && count)
@@ -529,7 +571,8 @@ int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params)
     const bool automatic = (params->flags & SPK_FLAG_AUTO_TRACER) && ctx->tracer_choice == 1 &&
                            params->accum_mode == SPK_ACCUM_SUM && ((params->flags >> 8) & 3u) == 0u;
     // a zero-iteration bounce loop has nothing to queue: the megakernel handles it
-    const bool wavefront = ((params->flags & SPK_FLAG_WAVEFRONT) || automatic) && params->max_bounce != 0u;
+    const bool wavefront = ((params->flags & SPK_FLAG_WAVEFRONT) || automatic) && params->max_bounce != 0u &&
+                           !(params->flags & SPK_FLAG_SPATIAL_DENOISE);
     int rc = wavefront ? launch_render_wavefront(ctx, params) : launch_render(ctx, params);
     if (rc != SPK_OK)
     {

@@ -759,6 +759,8 @@ void CudaRenderer::Render()
     p.max_bounce = render_config_.max_bounce;
     p.output_limit = 6.f; // CameraRenderProxy::OutputLimit (CameraRenderProxy.h:16)
     p.accum_mode = SPK_ACCUM_RUNNING_AVERAGE; // the reference's temporal lerp (CPURenderer.cpp:530-544)
+    // RenderConfig::spatial_denoise: g-buffer + neighbour fill per sample (CPURenderer.cpp:511-526)
+    p.flags = render_config_.spatial_denoise ? SPK_FLAG_SPATIAL_DENOISE : 0u;
     rc = rc == SPK_OK ? spk_cuda_render(ctx_, &p) : rc;
     if (rc != SPK_OK)
     {

@@ -161,3 +161,27 @@ def test_port_equals_reference_larger(port, name, n_rays, spp):
     ar, _ = ref.render(desc, cam, w, h, 5, spp, max_bounce=bounce)
     ap, _ = port.render(desc, cam, w, h, 5, spp, max_bounce=bounce)
     assert_same_bits(ap, ar, f"{name} accumulation image")
+
+
+def test_spatial_denoise_port_equals_reference():
+    """a15: SpatialDenoisePixel + temporal lerp (CPURenderer.cpp:452-552); the room scene has invalid pixels to fill"""
+    if not (O.available("port") and O.available("reference")):
+        pytest.skip("needs both oracle libraries")
+    from sparkle_b200 import scenes
+    from sparkle_b200.scene import orbit_camera
+    w, h = 96, 64
+    sb, camkw = scenes.room(num_objects=20, tex=32)
+    desc = sb.finalize()
+    cam = orbit_camera(w, h, **camkw)
+    out = {}
+    for kind in ("port", "reference"):
+        orc = O.Oracle(kind)
+        plain, _ = orc.render(desc, cam, w, h, 0, 3, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1)
+        den, cum = orc.render(desc, cam, w, h, 0, 3, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1,
+                              flags=A.FLAG_SPATIAL_DENOISE)
+        assert cum == 3
+        out[kind] = (plain, den)
+    assert (out["port"][0] != out["port"][1]).any(), "the scene must exercise the fill"
+    assert np.array_equal(out["port"][1], out["reference"][1])
+    with pytest.raises(RuntimeError):
+        O.Oracle("port").render(desc, cam, w, h, 0, 1, flags=A.FLAG_SPATIAL_DENOISE)  # sum mode: not the reference's pass

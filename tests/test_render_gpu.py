@@ -158,3 +158,28 @@ def test_wavefront_equals_megakernel(name, bounce, spp, oracle, monkeypatch):
     with pytest.raises(A.SpkError):
         ctx.render(0, 1, accum_mode=A.ACCUM_RUNNING_AVERAGE, flags=A.FLAG_WAVEFRONT)
     ctx.close()
+
+
+def test_spatial_denoise(oracle):
+    """a15 (SPK_FLAG_SPATIAL_DENOISE): g-buffer sample, 8-neighbour fill of invalid pixels, running average"""
+    w, h = 96, 64
+    sb, desc, cam = build("room", w, h)
+    ref, cum = oracle.render(desc, cam, w, h, 0, 3, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1,
+                             flags=A.FLAG_SPATIAL_DENOISE)
+    plain, _ = oracle.render(desc, cam, w, h, 0, 3, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1)
+    ctx = CudaContext(w, h)
+    ctx.upload_scene(desc)
+    ctx.set_camera(cam)
+    ctx.render(0, 2, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, flags=A.FLAG_SPATIAL_DENOISE)
+    ctx.render(2, 1, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, flags=A.FLAG_SPATIAL_DENOISE)
+    gpu = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    assert ctx.accum_sample_count() == 3 and cum == 3
+    changed = (ref != plain).any(-1)
+    assert changed.any(), "the scene must exercise the fill"
+    m = image_metrics(gpu, ref)
+    assert m["frac_gt_1e4"] < 0.01, m
+    # the filled pixels carry the neighbour's colour exactly as in the reference
+    rel = np.abs(gpu[..., :3] - ref[..., :3]).sum(-1) / np.maximum(ref[..., :3].sum(-1), 1e-3)
+    assert (rel[changed] < 1e-4).mean() > 0.9, rel[changed]
+    assert np.array_equal(gpu[..., 3][changed], ref[..., 3][changed])
+    ctx.close()
