@@ -59,104 +59,41 @@ __global__ void __launch_bounds__(kTraceThreads)
 // ---- persistent, warp-converged form (spk_traverse_warp.cuh): the default for ray batches ----
 constexpr int kPersistWarps = 4;
 
-template <bool CULL, bool COUNT, int LEAF_VOTE>
+template <bool CULL, bool COUNT, int REFILL>
 __global__ void __launch_bounds__(kPersistWarps * 32)
     trace_persistent_kernel(const DScene sc, const float4 *__restrict__ rays, unsigned long long n,
                             float *__restrict__ hits, unsigned long long *__restrict__ counters,
                             unsigned long long *__restrict__ next_ray)
 {
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    __shared__ uint32_t s_stack[kPersistWarps * kSmemStack * 32];
-    LaneStack stack;
-    stack.sm = s_stack + (threadIdx.x >> 5) * (kSmemStack * 32) + (threadIdx.x & 31u);
-    LaneState s;
+    __shared__ uint32_t s_lane_words[kPersistWarps * kLaneSmemWords * 32];
     TraceCounters cnt{0, 0, 0, 0};
-    unsigned long long ray_id = ~0ull;
-    bool active = false;
-    bool exhausted = false; // warp-uniform: the global counter has passed n
-    const float4 *__restrict__ pairs = sc.pairs;
-    for (;;)
-    {
-        // ---- refill idle lanes from the global ray counter
-        unsigned idle = __ballot_sync(0xffffffffu, !active);
-        if (idle && exhausted)
-        {
-            if (idle == 0xffffffffu)
+    auto write_hit = [&](unsigned long long id, const Hit &best) {
+        float *o = hits + 5 * id;
+        o[0] = best.t;
+        o[1] = best.u;
+        o[2] = best.v;
+        uint32_t prim = best.inst == SPK_INVALID_ID ? SPK_INVALID_ID : __ldg(&sc.instances[best.inst].prim);
+        o[3] = __uint_as_float(prim);
+        o[4] = __uint_as_float(best.face);
+    };
+    warp_trace_loop<CULL, COUNT, REFILL>(
+        sc, n, next_ray, s_lane_words, cnt,
+        [&](unsigned long long id, V3 &o, V3 &d) {
+            if (sc.num_instances == 0)
             {
-                break;
+                Hit miss{SPK_FLT_MAX, 0.f, 0.f, SPK_INVALID_ID, SPK_INVALID_ID}; // empty scene: every ray misses
+                write_hit(id, miss);
+                return false;
             }
-        }
-        else if (idle)
-        {
-            unsigned long long base = 0;
-            int leader = __ffs(idle) - 1;
-            if ((int)lane == leader)
-            {
-                base = atomicAdd(next_ray, (unsigned long long)__popc(idle));
-            }
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (!active)
-            {
-                unsigned long long id = base + __popc(idle & lt_mask);
-                if (id < n && sc.num_instances != 0)
-                {
-                    float4 ro = __ldg(rays + 2 * id), rd = __ldg(rays + 2 * id + 1);
-                    lane_begin<CULL>(sc, s, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z));
-                    ray_id = id;
-                    active = true;
-                }
-                else if (id < n)
-                {
-                    float *o = hits + 5 * id; // empty scene: every ray misses
-                    o[0] = SPK_FLT_MAX;
-                    o[1] = 0.f;
-                    o[2] = 0.f;
-                    o[3] = __uint_as_float(SPK_INVALID_ID);
-                    o[4] = __uint_as_float(SPK_INVALID_ID);
-                }
-            }
-            exhausted = base + __popc(idle) >= n;
-            if (base >= n && !__any_sync(0xffffffffu, active))
-            {
-                break;
-            }
-        }
-        // ---- inner phase
-        for (;;)
-        {
-            bool inner = active && (s.top & 15u) == 0u;
-            unsigned m_inner = __ballot_sync(0xffffffffu, inner);
-            unsigned m_leaf = __ballot_sync(0xffffffffu, active && !inner);
-            if (m_inner == 0u || __popc(m_leaf) >= LEAF_VOTE)
-            {
-                break;
-            }
-            if (inner)
-            {
-                active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
-            }
-        }
-        // ---- leaf phase (one item per lane); finished lanes write their hit
-        if (active && (s.top & 15u) != 0u)
-        {
-            active = lane_leaf_step<CULL, COUNT>(sc, s, stack, cnt);
-        }
-        // lanes that ran out of stack in either phase
-        if (!active && ray_id != ~0ull)
-        {
-            float *o = hits + 5 * ray_id;
-            o[0] = s.best.t;
-            o[1] = s.best.u;
-            o[2] = s.best.v;
-            uint32_t prim = s.best.inst == SPK_INVALID_ID ? SPK_INVALID_ID : __ldg(&sc.instances[s.best.inst].prim);
-            o[3] = __uint_as_float(prim);
-            o[4] = __uint_as_float(s.best.face);
-            ray_id = ~0ull;
-        }
-    }
+            float4 ro = __ldg(rays + 2 * id), rd = __ldg(rays + 2 * id + 1);
+            o = mk(ro.x, ro.y, ro.z);
+            d = mk(rd.x, rd.y, rd.z);
+            return true;
+        },
+        write_hit);
     if (COUNT)
     {
+        const unsigned lane = threadIdx.x & 31u;
         uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
 #pragma unroll
         for (int k = 0; k < 4; k++)
@@ -171,19 +108,19 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
 }
 } // namespace
 
-static int leaf_vote_setting()
+static int refill_setting()
 {
     static int v = [] {
-        const char *e = getenv("SPK_LEAF_VOTE");
+        const char *e = getenv("SPK_REFILL");
         return e ? atoi(e) : 16;
     }();
     return v;
 }
 
-template <bool CULL, bool COUNT, int VOTE>
+template <bool CULL, bool COUNT, int REFILL>
 static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, float *hits)
 {
-    auto kernel = trace_persistent_kernel<CULL, COUNT, VOTE>;
+    auto kernel = trace_persistent_kernel<CULL, COUNT, REFILL>;
     static int blocks_per_sm = 0, sms = 0;
     if (blocks_per_sm == 0)
     {
@@ -229,21 +166,18 @@ int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *
             trace_closest_kernel<true, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
     }
     else if (exact && count)
-        rc = launch_persistent<false, true, 16>(ctx, rays, n, hits);
+        rc = launch_persistent<false, true, 4>(ctx, rays, n, hits);
     else if (exact)
-        rc = launch_persistent<false, false, 16>(ctx, rays, n, hits);
+        rc = launch_persistent<false, false, 4>(ctx, rays, n, hits);
     else if (count)
-        rc = launch_persistent<true, true, 16>(ctx, rays, n, hits);
+        rc = launch_persistent<true, true, 4>(ctx, rays, n, hits);
     else
     {
-        switch (leaf_vote_setting())
+        switch (refill_setting())
         {
         case 1: rc = launch_persistent<true, false, 1>(ctx, rays, n, hits); break;
-        case 4: rc = launch_persistent<true, false, 4>(ctx, rays, n, hits); break;
         case 8: rc = launch_persistent<true, false, 8>(ctx, rays, n, hits); break;
-        case 12: rc = launch_persistent<true, false, 12>(ctx, rays, n, hits); break;
-        case 24: rc = launch_persistent<true, false, 24>(ctx, rays, n, hits); break;
-        case 32: rc = launch_persistent<true, false, 32>(ctx, rays, n, hits); break;
+        case 4: rc = launch_persistent<true, false, 4>(ctx, rays, n, hits); break;
         default: rc = launch_persistent<true, false, 16>(ctx, rays, n, hits); break;
         }
     }

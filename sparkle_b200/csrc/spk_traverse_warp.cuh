@@ -1,17 +1,23 @@
 /*
- * spk_traverse_warp.cuh — warp-converged form of the traversal in spk_traverse.cuh for incoherent ray batches.
+ * spk_traverse_warp.cuh — persistent, warp-scheduled form of the traversal in spk_traverse.cuh for ray batches and
+ * ray queues (spk_trace.cu, spk_wavefront.cu).
  *
  * Same arithmetic, same visit order per ray (so the same closest hit, bit for bit); what changes is how the 32 lanes of
  * a warp are kept on the same instruction. spk_traverse.cuh lets every lane run its own nested while loops; on
- * incoherent rays ncu showed 3.5 of 32 lanes active per issued instruction (profiles/r1_trace_simple.txt). Here each lane
- * is a small state machine {top, sp, level} and the warp alternates between two phases it votes on:
- *   inner phase  every lane whose `top` is an inner node does one step (fetch the 64-byte child pair, two slab tests,
- *                descend / push / pop); repeated while at least one lane has inner work and fewer than kLeafVote
- *                lanes are parked on a leaf;
- *   leaf phase   every lane parked on a leaf item handles it: BLAS leaf -> its triangles, TLAS leaf -> enter the next
- *                instance (sphere test, or ray into object space and BLAS root), sentinel -> back to world space.
+ * incoherent rays ncu showed 3.5 of 32 lanes active per issued instruction (profiles/r1_trace_thread_per_ray_ncu.txt).
+ * Here each lane is a small state machine {top, sp, inst} in one of three states, and every iteration the warp runs the
+ * step of the state MOST lanes are in (majority vote; lanes in the other states wait and accumulate):
+ *   inner   one bvh::v2 inner step: fetch the 64-byte child pair, two slab tests, descend / push / pop
+ *   tri     ONE triangle of the BLAS leaf in `top` (a leaf of n triangles is n steps, so short leaves do not wait for
+ *           long ones), then the rest of the leaf or pop
+ *   tlas    one primitive of the TLAS leaf in `top`: sphere test, or ray into object space and the BLAS root
+ * Leaving an instance (the sentinel on the stack) is folded into pop: the world-space slab constants are kept in shared
+ * memory per lane, so it costs six shared loads instead of three IEEE divisions in a step of its own.
  * Lanes that finish a ray take the next one from a global counter (persistent threads), so a warp never drains while
  * the batch has rays left.
+ * History (ncu, city scene, profiles/r1_wf_extend_city_ncu.txt): the first version voted only between "inner" and "any
+ * leaf" and ran the three leaf kinds one after the other with 4.7-6.3 lanes each; safe_inverse alone was 11.5 % of the
+ * issued instructions at 4.7 lanes.
  */
 #pragma once
 #include "spk_traverse.cuh"
@@ -21,14 +27,14 @@ namespace spk
 constexpr uint32_t kSentinel = 0xFFFFFFFFu; // stack marker: "leave the instance, back to the TLAS"
 constexpr int kWarpStack = 68;              // 32 TLAS + 1 leaf remainder + 1 sentinel + 32 BLAS (+2 spare)
 constexpr int kSmemStack = 24;              // entries per lane kept in shared memory; deeper ones spill to local memory
+constexpr int kLaneSmemWords = kSmemStack + 6; // + the world-space slab constants
 
-// Per-lane traversal stack. A stack in local memory shares L1 with the node fetches, and 32 lanes at 32 different
-// depths touch 32 different lines per push or pop (ncu: L1/TEX at 86 % of peak). The first kSmemStack
-// entries therefore live in shared memory as [depth][lane]: bank = lane whatever the depths are, so every push or pop
-// is one conflict-free wavefront.
+// Per-lane traversal stack. The first kSmemStack entries live in shared memory as [depth][lane]: bank = lane whatever
+// the depths are, so every push or pop is one conflict-free wavefront (a local-memory stack touches up to 32 lines
+// when 32 lanes are at 32 depths, and shares L1 with the node fetches).
 struct LaneStack
 {
-    uint32_t *sm; // this lane's column: sm[depth * 32]
+    uint32_t *sm; // this lane's column: sm[depth * 32]; rows kSmemStack.. hold the world slab constants
     uint32_t deep[kWarpStack - kSmemStack];
     __device__ __forceinline__ void push(int &sp, uint32_t v)
     {
@@ -56,19 +62,27 @@ struct LaneState
     SlabRay sr;     // slab constants of the current level
     Hit best;
     float slack_abs;
-    uint32_t top;   // current node word (inner / leaf) or kSentinel
+    uint32_t top;   // current node word (inner / leaf)
     int sp;
     uint32_t inst;  // instance being traversed, SPK_INVALID_ID at TLAS level
     float f0, f1, f2, f3; // row 0 of that instance's forward matrix (world_t needs only p.x, Ray.h:43-47)
 };
 
-template <bool CULL> __device__ __forceinline__ void lane_begin(const DScene &sc, LaneState &s, V3 wo, V3 wd)
+template <bool CULL>
+__device__ __forceinline__ void lane_begin(const DScene &sc, LaneState &s, LaneStack &stack, V3 wo, V3 wd)
 {
     s.wo = wo;
     s.wd = wd;
     s.lo = wo;
     s.ld = wd;
     s.sr = make_slab_ray(wo, wd);
+    float *w = reinterpret_cast<float *>(stack.sm) + kSmemStack * 32;
+    w[0] = s.sr.ix;
+    w[32] = s.sr.iy;
+    w[64] = s.sr.iz;
+    w[96] = s.sr.ox;
+    w[128] = s.sr.oy;
+    w[160] = s.sr.oz;
     s.best.t = SPK_FLT_MAX;
     s.best.u = 0.f;
     s.best.v = 0.f;
@@ -80,15 +94,35 @@ template <bool CULL> __device__ __forceinline__ void lane_begin(const DScene &sc
     s.inst = SPK_INVALID_ID;
 }
 
-// pop the next item; returns false when the stack is empty (ray finished)
+// pop the next item; returns false when the stack is empty (ray finished). A sentinel means BLAS::IntersectInternal
+// returned: back to the world ray (its slab constants come from shared memory), then pop again.
 __device__ __forceinline__ bool lane_pop(LaneState &s, LaneStack &stack)
 {
-    if (s.sp == 0)
+    for (;;)
     {
-        return false;
+        if (s.sp == 0)
+        {
+            return false;
+        }
+        s.top = stack.pop(s.sp);
+        if (s.top != kSentinel)
+        {
+            return true;
+        }
+        s.inst = SPK_INVALID_ID;
+        s.lo = s.wo;
+        s.ld = s.wd;
+        const float *w = reinterpret_cast<const float *>(stack.sm) + kSmemStack * 32;
+        s.sr.ix = w[0];
+        s.sr.iy = w[32];
+        s.sr.iz = w[64];
+        s.sr.ox = w[96];
+        s.sr.oy = w[128];
+        s.sr.oz = w[160];
+        s.sr.nx = signbit(s.wd.x);
+        s.sr.ny = signbit(s.wd.y);
+        s.sr.nz = signbit(s.wd.z);
     }
-    s.top = stack.pop(s.sp);
-    return true;
 }
 
 // one bvh::v2 inner step (identical to the loop body of traverse_tree); returns false when the ray is finished
@@ -136,36 +170,30 @@ __device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs
     return lane_pop(s, stack);
 }
 
-// handle the leaf item in `top`; returns false when the ray is finished
-template <bool CULL, bool COUNT>
-__device__ __forceinline__ bool lane_leaf_step(const DScene &sc, LaneState &s, LaneStack &stack, TraceCounters &cnt)
+// BLAS leaf in `top`: IntersectTriangle on prim_ids[first], then the rest of the leaf (same order as the leaf loop)
+template <bool COUNT>
+__device__ __forceinline__ bool lane_tri_step(const DScene &sc, LaneState &s, LaneStack &stack, TraceCounters &cnt)
 {
-    if (s.top == kSentinel)
-    {
-        // BLAS::IntersectInternal returned: back to the world ray
-        s.inst = SPK_INVALID_ID;
-        s.lo = s.wo;
-        s.ld = s.wd;
-        s.sr = make_slab_ray(s.wo, s.wd);
-        return lane_pop(s, stack);
-    }
     const uint32_t first = s.top >> 4, count = s.top & 15u;
-    if (s.inst != SPK_INVALID_ID)
+    const float fwd_row0[4] = {s.f0, s.f1, s.f2, s.f3};
+    if (COUNT)
     {
-        // BLAS leaf: IntersectTriangle over prim_ids[first, first+count)
-        const float fwd_row0[4] = {s.f0, s.f1, s.f2, s.f3};
-        const float4 *__restrict__ tris = sc.tris;
-        for (uint32_t k = first; k < first + count; k++)
-        {
-            if (COUNT)
-            {
-                cnt.tri_tests++;
-            }
-            intersect_triangle(tris + size_t(k) * 3, s.lo, s.ld, s.wo, s.wd, fwd_row0, s.inst, s.best);
-        }
-        return lane_pop(s, stack);
+        cnt.tri_tests++;
     }
-    // TLAS leaf: primitives_[first] now, the rest of the leaf afterwards (same order as the reference's leaf loop)
+    intersect_triangle(sc.tris + size_t(first) * 3, s.lo, s.ld, s.wo, s.wd, fwd_row0, s.inst, s.best);
+    if (count > 1u)
+    {
+        s.top = ((first + 1u) << 4) | (count - 1u);
+        return true;
+    }
+    return lane_pop(s, stack);
+}
+
+// TLAS leaf in `top`: primitives_[first] now, the rest of the leaf afterwards (same order as the reference's leaf loop)
+template <bool COUNT>
+__device__ __forceinline__ bool lane_tlas_step(const DScene &sc, LaneState &s, LaneStack &stack, TraceCounters &cnt)
+{
+    const uint32_t first = s.top >> 4, count = s.top & 15u;
     if (count > 1u)
     {
         stack.push(s.sp, ((first + 1u) << 4) | (count - 1u));
@@ -207,5 +235,89 @@ __device__ __forceinline__ bool lane_leaf_step(const DScene &sc, LaneState &s, L
     stack.push(s.sp, kSentinel);
     s.top = __ldg(&in->root);
     return true;
+}
+
+/*
+ * The persistent loop of one warp. `cursor` is the global ray counter, n the number of rays; fetch(id, o, d) loads ray
+ * id and returns false to skip it, store(id, best) writes its closest hit. REFILL: idle lanes wait until this many are
+ * idle (or nothing else is left to do) before one lane fetches a block of ray ids with a single atomic.
+ */
+template <bool CULL, bool COUNT, int REFILL, typename Fetch, typename Store>
+__device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long long n, unsigned long long *cursor,
+                                                uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch, Store &&store)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    LaneStack stack;
+    stack.sm = s_lane_words + (threadIdx.x >> 5) * (kLaneSmemWords * 32) + lane;
+    LaneState s;
+    s.top = 0u;
+    s.inst = SPK_INVALID_ID;
+    unsigned long long ray_id = ~0ull;
+    bool active = false;
+    bool exhausted = false; // warp-uniform: the global counter has passed n
+    const float4 *__restrict__ pairs = sc.pairs;
+    for (;;)
+    {
+        // ---- refill idle lanes from the global ray counter
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle == 0xffffffffu && exhausted)
+        {
+            break;
+        }
+        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xffffffffu))
+        {
+            unsigned long long base = 0;
+            const int leader = __ffs(idle) - 1;
+            if ((int)lane == leader)
+            {
+                base = atomicAdd(cursor, (unsigned long long)__popc(idle));
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active)
+            {
+                unsigned long long id = base + __popc(idle & lt_mask);
+                V3 o, d;
+                if (id < n && fetch(id, o, d))
+                {
+                    lane_begin<CULL>(sc, s, stack, o, d);
+                    ray_id = id;
+                    active = true;
+                }
+            }
+            exhausted = base + __popc(idle) >= n;
+        }
+        // ---- majority vote: the state most lanes are in runs one step
+        const bool is_inner = active && (s.top & 15u) == 0u;
+        const bool is_tri = active && !is_inner && s.inst != SPK_INVALID_ID;
+        const bool is_tlas = active && !is_inner && s.inst == SPK_INVALID_ID;
+        const int c_inner = __popc(__ballot_sync(0xffffffffu, is_inner));
+        const int c_tri = __popc(__ballot_sync(0xffffffffu, is_tri));
+        const int c_tlas = __popc(__ballot_sync(0xffffffffu, is_tlas));
+        if (c_inner >= c_tri && c_inner >= c_tlas)
+        {
+            if (is_inner)
+            {
+                active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
+            }
+        }
+        else if (c_tri >= c_tlas)
+        {
+            if (is_tri)
+            {
+                active = lane_tri_step<COUNT>(sc, s, stack, cnt);
+            }
+        }
+        else if (is_tlas)
+        {
+            active = lane_tlas_step<COUNT>(sc, s, stack, cnt);
+        }
+        // lanes whose stack ran empty: the ray is finished
+        if (!active && ray_id != ~0ull)
+        {
+            store(ray_id, s.best);
+            ray_id = ~0ull;
+        }
+    }
 }
 } // namespace spk

@@ -37,7 +37,8 @@ struct WfCtrl
 {
     uint32_t n_queue[2]; // entries in queue[0] / queue[1]
     uint32_t n_regen;    // entries in the regen list
-    uint32_t next_ray;   // wf_extend's queue cursor
+    uint32_t pad;
+    unsigned long long next_ray; // wf_extend's queue cursor
     unsigned long long work_next, work_total; // (pixel, sample) items handed out so far / in this call
     unsigned long long rays;                   // segments traced in this call
 };
@@ -145,88 +146,31 @@ __global__ void wf_advance_kernel(WfState st, uint32_t cur, unsigned long long *
 }
 
 // ---- extend: closest hit of every queued ray; the loop of trace_persistent_kernel (spk_trace.cu) over an indirect queue
-template <bool CULL, bool COUNT, int LEAF_VOTE>
+template <bool CULL, bool COUNT, int REFILL>
 __global__ void __launch_bounds__(kExtendWarps * 32)
     wf_extend_kernel(const DScene sc, WfState st, uint32_t q, unsigned long long *__restrict__ counters)
 {
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const uint32_t n = st.ctrl->n_queue[q];
+    __shared__ uint32_t s_lane_words[kExtendWarps * kLaneSmemWords * 32];
     const uint32_t *__restrict__ queue = st.queue[q];
     const float4 *__restrict__ rays = st.rays;
-    uint32_t *next_ray = &st.ctrl->next_ray;
-    __shared__ uint32_t s_stack[kExtendWarps * kSmemStack * 32];
-    LaneStack stack;
-    stack.sm = s_stack + (threadIdx.x >> 5) * (kSmemStack * 32) + (threadIdx.x & 31u);
-    LaneState s;
     TraceCounters cnt{0, 0, 0, 0};
-    uint32_t slot = kEmptySlot;
-    bool active = false;
-    bool exhausted = false; // warp-uniform: the queue cursor has passed n
-    const float4 *__restrict__ pairs = sc.pairs;
-    for (;;)
-    {
-        unsigned idle = __ballot_sync(0xffffffffu, !active);
-        if (idle && exhausted)
-        {
-            if (idle == 0xffffffffu)
-            {
-                break;
-            }
-        }
-        else if (idle)
-        {
-            uint32_t base = 0;
-            int leader = __ffs(idle) - 1;
-            if ((int)lane == leader)
-            {
-                base = atomicAdd(next_ray, (uint32_t)__popc(idle));
-            }
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (!active)
-            {
-                uint32_t id = base + __popc(idle & lt_mask);
-                if (id < n)
-                {
-                    slot = __ldg(queue + id);
-                    float4 ro = rays[2 * size_t(slot)], rd = rays[2 * size_t(slot) + 1];
-                    lane_begin<CULL>(sc, s, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z));
-                    active = true;
-                }
-            }
-            exhausted = base + __popc(idle) >= n;
-            if (base >= n && !__any_sync(0xffffffffu, active))
-            {
-                break;
-            }
-        }
-        for (;;)
-        {
-            bool inner = active && (s.top & 15u) == 0u;
-            unsigned m_inner = __ballot_sync(0xffffffffu, inner);
-            unsigned m_leaf = __ballot_sync(0xffffffffu, active && !inner);
-            if (m_inner == 0u || __popc(m_leaf) >= LEAF_VOTE)
-            {
-                break;
-            }
-            if (inner)
-            {
-                active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
-            }
-        }
-        if (active && (s.top & 15u) != 0u)
-        {
-            active = lane_leaf_step<CULL, COUNT>(sc, s, stack, cnt);
-        }
-        if (!active && slot != kEmptySlot)
-        {
-            st.hit[slot] = make_float4(s.best.t, s.best.u, s.best.v, __uint_as_float(s.best.inst));
-            st.face[slot] = s.best.face;
-            slot = kEmptySlot;
-        }
-    }
+    warp_trace_loop<CULL, COUNT, REFILL>(
+        sc, st.ctrl->n_queue[q], &st.ctrl->next_ray, s_lane_words, cnt,
+        [&](unsigned long long id, V3 &o, V3 &d) {
+            const uint32_t slot = __ldg(queue + id);
+            float4 ro = rays[2 * size_t(slot)], rd = rays[2 * size_t(slot) + 1];
+            o = mk(ro.x, ro.y, ro.z);
+            d = mk(rd.x, rd.y, rd.z);
+            return true;
+        },
+        [&](unsigned long long id, const Hit &best) {
+            const uint32_t slot = __ldg(queue + id);
+            st.hit[slot] = make_float4(best.t, best.u, best.v, __uint_as_float(best.inst));
+            st.face[slot] = best.face;
+        });
     if (COUNT)
     {
+        const unsigned lane = threadIdx.x & 31u;
         uint32_t v[4] = {cnt.node_visits, cnt.tri_tests, cnt.inst_visits, cnt.sphere_tests};
 #pragma unroll
         for (int k = 0; k < 4; k++)
@@ -470,7 +414,7 @@ static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st)
 template <bool CULL, bool COUNT>
 static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t sample_count)
 {
-    auto extend = wf_extend_kernel<CULL, COUNT, 16>;
+    auto extend = wf_extend_kernel<CULL, COUNT, 4>;
     static int blocks_per_sm = 0, sms = 0;
     if (blocks_per_sm == 0)
     {
