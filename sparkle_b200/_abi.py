@@ -138,6 +138,11 @@ HOST_SYMBOLS = {
     "spk_host_app_save_screenshot": (C.c_int, [C.c_void_p, C.c_char_p]),
     "spk_host_app_move_primitive": (C.c_int, [C.c_void_p, u32, f32, f32, f32]),
     "spk_host_parse_pipeline": (C.c_int, [C.c_char_p]),
+    "spk_host_app_set_orbit": (None, [C.c_void_p, f32, f32, f32, f32, f32, f32]),
+    "spk_host_scene_load_gltf": (C.c_void_p, [C.c_char_p, C.c_int]),
+    "spk_host_scene_desc": (C.POINTER(SceneDesc), [C.c_void_p]),
+    "spk_host_scene_free": (None, [C.c_void_p]),
+    "spk_host_gltf_probe": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_uint64)]),
 }
 
 _libs = {}

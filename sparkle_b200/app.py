@@ -66,6 +66,20 @@ class HostApp:
             raise IndexError(primitive)
 
 
+    def set_orbit(self, center=(0, 0, 0), radius=25.0, pitch=10.0, yaw=-20.0):
+        """OrbitCameraComponent::Setup; the accumulation restarts on the next frame"""
+        self.lib.spk_host_app_set_orbit(self.handle, *[float(x) for x in center], float(radius), float(pitch), float(yaw))
+
+
+def gltf_probe(path, instancing=False):
+    """counters of GLTFLoader-style ingestion of `path` (sparkle_b200/host/gltf_loader.h)"""
+    out = (C.c_uint64 * 7)()
+    if A.host_lib().spk_host_gltf_probe(str(path).encode(), int(instancing), out) != 0:
+        raise RuntimeError(A.host_lib().spk_host_last_error().decode())
+    keys = ("nodes", "primitives", "unique_meshes", "materials", "textures", "instanced_triangles", "unique_triangles")
+    return dict(zip(keys, [int(v) for v in out]))
+
+
 def main(argv):
     output = "screenshot.png"
     args = []

@@ -13,6 +13,7 @@
 #include <sstream>
 
 #include "bvh_builder.h"
+#include "gltf_loader.h"
 
 namespace sparkle_cuda
 {
@@ -67,6 +68,7 @@ Vec3 Apply(const Mat3 &r, Vec3 v)
 } // namespace
 
 const std::string &LastError() { return g_last_error; }
+void SetLastError(const std::string &msg) { LogError(msg); } // other translation units of the host library
 
 // ---- RenderConfig ------------------------------------------------------------------------------------------------------
 static const char *kPipelineNames[] = {"Cpu", "Gpu", "Forward", "Deferred", "Cuda"};
@@ -512,6 +514,22 @@ uint32_t SceneProxy::AddMeshPrimitive(uint32_t mesh, uint32_t material, const Tr
     p.mesh = mesh;
     p.material = material;
     t.Matrices(p.fwd, p.inv);
+    primitives_.push_back(p);
+    std::array<float, 6> box;
+    WorldBox(p.fwd, impl_->meshes[mesh].lo, impl_->meshes[mesh].hi, box);
+    world_boxes_.push_back(box);
+    changes_.emplace_back(PrimitiveChangeType::New, NumPrimitives() - 1);
+    return NumPrimitives() - 1;
+}
+
+uint32_t SceneProxy::AddMeshPrimitiveMatrix(uint32_t mesh, uint32_t material, const float fwd[12], const float inv[12])
+{
+    SpkPrimitiveDesc p{};
+    p.kind = SPK_PRIM_MESH;
+    p.mesh = mesh;
+    p.material = material;
+    memcpy(p.fwd, fwd, sizeof(p.fwd));
+    memcpy(p.inv, inv, sizeof(p.inv));
     primitives_.push_back(p);
     std::array<float, 6> box;
     WorldBox(p.fwd, impl_->meshes[mesh].lo, impl_->meshes[mesh].hi, box);
@@ -1050,11 +1068,16 @@ SpkHostApp *spk_host_app_create(const char *args, int device)
         tokens.push_back(t);
     }
     std::string scene_name = "testscene";
+    GltfOptions gltf_options;
     for (size_t k = 0; k + 1 < tokens.size(); k += 2)
     {
         if (tokens[k] == "--scene")
         {
             scene_name = tokens[k + 1];
+        }
+        else if (tokens[k] == "--gltf_instancing")
+        {
+            gltf_options.instancing = tokens[k + 1] == "true" || tokens[k + 1] == "1";
         }
         else
         {
@@ -1066,11 +1089,23 @@ SpkHostApp *spk_host_app_create(const char *args, int device)
     {
         return nullptr;
     }
-    if (scene_name != "testscene" && scene_name != "empty")
+    const bool gltf = scene_name.size() > 5 && scene_name.compare(scene_name.size() - 5, 5, ".gltf") == 0;
+    if (scene_name != "testscene" && scene_name != "empty" && !gltf)
     {
+        LogError("unknown scene '" + scene_name + "' (testscene, empty or a .gltf path)");
         return nullptr;
     }
-    if (scene_name == "testscene")
+    if (gltf)
+    {
+        // SceneManager::LoadScene -> GLTFLoader::Load (AppFramework.cpp:200-205: a failed load logs and fails init)
+        if (!LoadGltf(scene_name, app->scene, nullptr, gltf_options))
+        {
+            return nullptr;
+        }
+        app->scene.SetSky(Vec3{0.5f, 0.7f, 1.0f});
+        app->scene.GetCamera().SetupOrbit(Vec3{0, 0, 0}, 25.f, 10.f, -20.f);
+    }
+    else if (scene_name == "testscene")
     {
         BuildTestScene(app->scene);
     }
@@ -1141,6 +1176,11 @@ int spk_host_app_save_screenshot(SpkHostApp *app, const char *path)
         return -1;
     }
     return WritePng(path, img.data(), app->config.image_width, app->config.image_height) ? 0 : -1;
+}
+
+void spk_host_app_set_orbit(SpkHostApp *app, float cx, float cy, float cz, float radius, float pitch_deg, float yaw_deg)
+{
+    app->scene.GetCamera().SetupOrbit(Vec3{cx, cy, cz}, radius, pitch_deg, yaw_deg);
 }
 
 int spk_host_app_move_primitive(SpkHostApp *app, uint32_t primitive, float tx, float ty, float tz)

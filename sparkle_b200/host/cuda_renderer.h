@@ -148,6 +148,8 @@ public:
     uint32_t AddMetal(Vec3 color, float roughness);     // MetalMaterial.h:11-15
     uint32_t AddDielectric(float eta);                  // DieletricMaterial.h
     uint32_t AddMeshPrimitive(uint32_t mesh, uint32_t material, const Transform &t);
+    // the same with explicit rows 0..2 of the forward and inverse matrices (scene loaders: quaternion rotations, hierarchies)
+    uint32_t AddMeshPrimitiveMatrix(uint32_t mesh, uint32_t material, const float fwd[12], const float inv[12]);
     uint32_t AddSphere(Vec3 center, float radius, uint32_t material); // SpherePrimitive.cpp:22-38
     void MovePrimitive(uint32_t primitive, const Transform &t);       // records PrimitiveChangeType::Update
     void SetSky(Vec3 color);
@@ -240,7 +242,8 @@ void BuildTestScene(SceneProxy &scene);
 extern "C"
 {
 typedef struct SpkHostApp SpkHostApp;
-/* args: space-separated "--name value" pairs, e.g. "--pipeline cuda --width 96 --height 64 --max_spp 4 --scene testscene" */
+/* args: space-separated "--name value" pairs, e.g. "--pipeline cuda --width 96 --height 64 --max_spp 4 --scene testscene"
+ * --scene: testscene | empty | path/to/file.gltf (GLTFLoader semantics, gltf_loader.h) */
 SpkHostApp *spk_host_app_create(const char *args, int device);
 void spk_host_app_destroy(SpkHostApp *app);
 const char *spk_host_last_error(void);
@@ -253,6 +256,8 @@ uint32_t spk_host_app_cumulated_samples(SpkHostApp *app);
 int spk_host_app_read_linear(SpkHostApp *app, float *out, size_t floats);
 int spk_host_app_save_screenshot(SpkHostApp *app, const char *path);
 int spk_host_app_move_primitive(SpkHostApp *app, uint32_t primitive, float tx, float ty, float tz);
+/* OrbitCameraComponent::Setup on the app's camera (marks the pixels dirty: accumulation restarts) */
+void spk_host_app_set_orbit(SpkHostApp *app, float cx, float cy, float cz, float radius, float pitch_deg, float yaw_deg);
 /* Str2Enum probe: returns the enumerator value or -1 */
 int spk_host_parse_pipeline(const char *name);
 }

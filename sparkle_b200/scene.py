@@ -100,7 +100,7 @@ class SceneBuilder:
         corners = np.array([[x, y, z] for x in (lo[0], hi[0]) for y in (lo[1], hi[1]) for z in (lo[2], hi[2])], f32)
         wc = corners @ fwd[:, :3].T + fwd[:, 3]
         self.prims.append(dict(kind=A.PRIM_MESH, mesh=mesh_id, material=material, radius2=0.0, fwd=fwd, inv=inv,
-                               lo=wc.min(axis=0), hi=wc.max(axis=0)))
+                               lo=wc.min(axis=0), hi=wc.max(axis=0), trs=(translate, euler, scale)))
         return len(self.prims) - 1
 
     def add_sphere(self, center, radius, material):

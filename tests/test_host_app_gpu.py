@@ -73,3 +73,23 @@ def test_primitive_move_restarts_accumulation(oracle):
     ref, _ = oracle.render(a.scene, a.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
     assert rel_err(after, ref) <= 1e-3
     a.close()
+
+
+def test_gltf_scene_through_the_host_app(tmp_path, oracle):
+    """8f-1: --scene file.gltf -> GLTFLoader semantics -> CudaRenderer; the image equals the oracle's on the app's own
+    scene description"""
+    from sparkle_b200 import gltf_export, scenes
+    sb, cam = scenes.city(num_meshes=4, tris_per_mesh=800, num_instances=24)
+    path = gltf_export.write_gltf(sb, tmp_path / "city.gltf")
+    w, h, spp = 96, 64, 4
+    a = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 1 --spatial_denoise false "
+                    f"--scene {path} --gltf_instancing true")
+    a.set_orbit(center=(0, 0, 1.0), radius=30.0, pitch=25.0, yaw=-30.0)
+    a.run()
+    assert a.cumulated_samples == spp
+    gpu = a.read_linear()
+    ref, _ = oracle.render(a.scene, a.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
+    rel = np.abs(gpu[..., :3] - ref[..., :3]).sum(-1) / np.maximum(ref[..., :3].sum(-1), 1e-3)
+    assert rel.mean() <= 1e-3, rel.mean()
+    assert (gpu[..., :3].std() > 0.01)  # an actual picture, not a constant
+    a.close()
