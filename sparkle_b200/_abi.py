@@ -165,7 +165,8 @@ def _load(name, symbols):
 
 
 def cuda_lib():
-    return _load("libsparkle_cuda.so", CUDA_SYMBOLS)
+    # SPK_CUDA_LIB: an A/B build of the same library next to the default one (kernel experiments only)
+    return _load(os.environ.get("SPK_CUDA_LIB", "libsparkle_cuda.so"), CUDA_SYMBOLS)
 
 
 def host_lib():

@@ -158,6 +158,17 @@ __device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs
                 far_i = li;
             }
             stack.push(s.sp, far_i);
+#ifdef SPK_PREFETCH_FAR
+            if ((far_i & 15u) == 0u)
+            {
+                // the far child is visited after the near subtree: start its 64-byte pair on the way now
+#if SPK_PREFETCH_FAR == 2
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(pairs + size_t(far_i >> 4) * 4));
+#else
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(pairs + size_t(far_i >> 4) * 4));
+#endif
+            }
+#endif
         }
         s.top = near_i;
         return true;
