@@ -170,6 +170,16 @@ __device__ __forceinline__ float safe_inverse(float x)
     return fabsf(x) <= 1.1920929e-07f ? copysignf(SPK_FLT_MAX, x) : 1.f / x;
 }
 
+// One 256-bit read-only load (LDG.E.256 on sm_100a; PTX ld.global.nc.v8.f32, 32-byte aligned address). A 64-byte node
+// pair is two of these instead of four LDG.128: incoherent lanes cost one L1 wavefront per lane per load instruction,
+// and the ray-batch kernel sat at 0.88 wavefronts per clock per SM (L1/TEX 79-86 % busy) whatever the scheduling.
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b)
+{
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+
 struct Hit
 {
     float t, u, v;

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kTraceThreads)
 // ---- persistent, warp-converged form (spk_traverse_warp.cuh): the default for ray batches ----
 constexpr int kPersistWarps = 4;
 
-template <bool CULL, bool COUNT, int REFILL>
+template <bool CULL, bool COUNT, int VOTE>
 __global__ void __launch_bounds__(kPersistWarps * 32)
     trace_persistent_kernel(const DScene sc, const float4 *__restrict__ rays, unsigned long long n,
                             float *__restrict__ hits, unsigned long long *__restrict__ counters,
@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
         o[3] = __uint_as_float(prim);
         o[4] = __uint_as_float(best.face);
     };
-    warp_trace_loop<CULL, COUNT, REFILL>(
+    warp_trace_loop<CULL, COUNT, 16, VOTE>(
         sc, n, next_ray, s_lane_words, cnt,
         [&](unsigned long long id, V3 &o, V3 &d) {
             if (sc.num_instances == 0)
@@ -108,19 +108,19 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
 }
 } // namespace
 
-static int refill_setting()
+static int vote_setting()
 {
     static int v = [] {
-        const char *e = getenv("SPK_REFILL");
-        return e ? atoi(e) : 16;
+        const char *e = getenv("SPK_VOTE");
+        return e ? atoi(e) : 6;
     }();
     return v;
 }
 
-template <bool CULL, bool COUNT, int REFILL>
+template <bool CULL, bool COUNT, int VOTE>
 static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, float *hits)
 {
-    auto kernel = trace_persistent_kernel<CULL, COUNT, REFILL>;
+    auto kernel = trace_persistent_kernel<CULL, COUNT, VOTE>;
     static int blocks_per_sm = 0, sms = 0;
     if (blocks_per_sm == 0)
     {
@@ -166,19 +166,20 @@ int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *
             trace_closest_kernel<true, false><<<grid, block, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters);
     }
     else if (exact && count)
-        rc = launch_persistent<false, true, 4>(ctx, rays, n, hits);
+        rc = launch_persistent<false, true, 8>(ctx, rays, n, hits);
     else if (exact)
-        rc = launch_persistent<false, false, 4>(ctx, rays, n, hits);
+        rc = launch_persistent<false, false, 8>(ctx, rays, n, hits);
     else if (count)
-        rc = launch_persistent<true, true, 4>(ctx, rays, n, hits);
+        rc = launch_persistent<true, true, 8>(ctx, rays, n, hits);
     else
     {
-        switch (refill_setting())
+        switch (vote_setting())
         {
-        case 1: rc = launch_persistent<true, false, 1>(ctx, rays, n, hits); break;
-        case 8: rc = launch_persistent<true, false, 8>(ctx, rays, n, hits); break;
         case 4: rc = launch_persistent<true, false, 4>(ctx, rays, n, hits); break;
-        default: rc = launch_persistent<true, false, 16>(ctx, rays, n, hits); break;
+        case 8: rc = launch_persistent<true, false, 8>(ctx, rays, n, hits); break;
+        case 12: rc = launch_persistent<true, false, 12>(ctx, rays, n, hits); break;
+        case 16: rc = launch_persistent<true, false, 16>(ctx, rays, n, hits); break;
+        default: rc = launch_persistent<true, false, 6>(ctx, rays, n, hits); break;
         }
     }
     if (rc != SPK_OK)

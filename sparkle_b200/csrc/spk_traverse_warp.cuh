@@ -6,7 +6,7 @@
  * a warp are kept on the same instruction. spk_traverse.cuh lets every lane run its own nested while loops; on
  * incoherent rays ncu showed 3.5 of 32 lanes active per issued instruction (profiles/r1_trace_thread_per_ray_ncu.txt).
  * Here each lane is a small state machine {top, sp, inst} in one of three states, and every iteration the warp runs the
- * step of the state MOST lanes are in (majority vote; lanes in the other states wait and accumulate):
+ * inner step unless enough lanes (VOTE) have accumulated in one of the two leaf states, which then runs instead:
  *   inner   one bvh::v2 inner step: fetch the 64-byte child pair, two slab tests, descend / push / pop
  *   tri     ONE triangle of the BLAS leaf in `top` (a leaf of n triangles is n steps, so short leaves do not wait for
  *           long ones), then the rest of the leaf or pop
@@ -131,7 +131,9 @@ __device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs
                                                 TraceCounters &cnt)
 {
     const float4 *p = pairs + size_t(s.top >> 4) * 4;
-    float4 l0 = __ldg(p), l1 = __ldg(p + 1), r0 = __ldg(p + 2), r1 = __ldg(p + 3);
+    float4 l0, l1, r0, r1;
+    ldg256(p, l0, l1);
+    ldg256(p + 2, r0, r1);
     if (COUNT)
     {
         cnt.node_visits++;
@@ -158,17 +160,6 @@ __device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs
                 far_i = li;
             }
             stack.push(s.sp, far_i);
-#ifdef SPK_PREFETCH_FAR
-            if ((far_i & 15u) == 0u)
-            {
-                // the far child is visited after the near subtree: start its 64-byte pair on the way now
-#if SPK_PREFETCH_FAR == 2
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(pairs + size_t(far_i >> 4) * 4));
-#else
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(pairs + size_t(far_i >> 4) * 4));
-#endif
-            }
-#endif
         }
         s.top = near_i;
         return true;
@@ -253,7 +244,7 @@ __device__ __forceinline__ bool lane_tlas_step(const DScene &sc, LaneState &s, L
  * id and returns false to skip it, store(id, best) writes its closest hit. REFILL: idle lanes wait until this many are
  * idle (or nothing else is left to do) before one lane fetches a block of ray ids with a single atomic.
  */
-template <bool CULL, bool COUNT, int REFILL, typename Fetch, typename Store>
+template <bool CULL, bool COUNT, int REFILL, int VOTE, typename Fetch, typename Store>
 __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long long n, unsigned long long *cursor,
                                                 uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch, Store &&store)
 {
@@ -305,23 +296,28 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
         const int c_inner = __popc(__ballot_sync(0xffffffffu, is_inner));
         const int c_tri = __popc(__ballot_sync(0xffffffffu, is_tri));
         const int c_tlas = __popc(__ballot_sync(0xffffffffu, is_tlas));
-        if (c_inner >= c_tri && c_inner >= c_tlas)
-        {
-            if (is_inner)
-            {
-                active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
-            }
-        }
-        else if (c_tri >= c_tlas)
+        // a leaf state runs as soon as VOTE lanes wait in it (or nothing else can run); inner steps otherwise. A pure
+        // majority vote starves the rare state: on soup-1M 6 % of the steps are triangles, their lanes waited until they
+        // outnumbered the inner lanes, and inner steps ran with 13.7 lanes (profiles/r1_trace_majority_vote_ncu.txt)
+        const bool run_tri = c_tri >= VOTE || (c_inner == 0 && c_tri > 0 && c_tri >= c_tlas);
+        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (c_inner == 0 && c_tlas > 0));
+        if (run_tri)
         {
             if (is_tri)
             {
                 active = lane_tri_step<COUNT>(sc, s, stack, cnt);
             }
         }
-        else if (is_tlas)
+        else if (run_tlas)
         {
-            active = lane_tlas_step<COUNT>(sc, s, stack, cnt);
+            if (is_tlas)
+            {
+                active = lane_tlas_step<COUNT>(sc, s, stack, cnt);
+            }
+        }
+        else if (is_inner)
+        {
+            active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
         }
         // lanes whose stack ran empty: the ray is finished
         if (!active && ray_id != ~0ull)

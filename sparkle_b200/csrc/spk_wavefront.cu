@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(kExtendWarps * 32)
     const uint32_t *__restrict__ queue = st.queue[q];
     const float4 *__restrict__ rays = st.rays;
     TraceCounters cnt{0, 0, 0, 0};
-    warp_trace_loop<CULL, COUNT, REFILL>(
+    warp_trace_loop<CULL, COUNT, REFILL, 8>(
         sc, st.ctrl->n_queue[q], &st.ctrl->next_ray, s_lane_words, cnt,
         [&](unsigned long long id, V3 &o, V3 &d) {
             const uint32_t slot = __ldg(queue + id);
