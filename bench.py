@@ -302,7 +302,8 @@ def run_cuda(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "parallelism": f"spp-split x{world}", "l2": "flushed between steps (256 MB fill)",
                    "tracer": "wavefront" if use_wavefront else "megakernel",
-                   "tracer_choice_ms_4spp": {"megakernel": choose_ms[0], "wavefront": choose_ms[1]} if choose_ms else None,
+                   "megakernel_form": ctx.tracer_choice()[1],
+                   "tracer_choice_ms_8spp": {"megakernel": choose_ms[0], "wavefront": choose_ms[1]} if choose_ms else None,
                    "mrays_per_s": rays_total / (kernel_ms * 1e-3) / 1e6, "rays_per_path": rays_launch / paths_launch},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -310,7 +311,10 @@ def run_cuda(args):
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": peak_src, "kernel": ("wf_extend_kernel<CULL=true> (+ wf_shade/regen/advance; achieved is over the whole step)"
-                                if use_wavefront else "render_phased_kernel<CULL=true, 8 warps x 3 CTAs/SM>"),
+                                if use_wavefront else {831: "render_phased_kernel<CULL=true, 8 warps x 3 CTAs/SM>",
+                                      1162: "render_sorted_kernel<CULL=true, 16 warps x 2 CTAs/SM>",
+                                      1084: "render_sorted_kernel<CULL=true, 8 warps x 4 CTAs/SM>"}.get(
+                                         ctx.tracer_choice()[1], "render_phased_kernel")),
                      "alg_bytes_per_ray": alg_bytes / max(1.0, rays_launch),
                      "node_visits_per_ray": cst["node_visits"] / max(1, cst["rays"]),
                      "tri_tests_per_ray": cst["tri_tests"] / max(1, cst["rays"])},

@@ -256,11 +256,14 @@ int spk_cuda_set_camera(SpkContext *ctx, const SpkCamera *camera);
 int spk_cuda_reset_accumulation(SpkContext *ctx);
 /* CPURenderer::BasePass + temporal accumulate (CPURenderer.cpp:419-450, 530-544) for sample_count samples. */
 int spk_cuda_render(SpkContext *ctx, const SpkRenderParams *params);
-/* Times a few samples per pixel of the current scene and camera with the megakernel and with the wavefront tracer
- * (CUDA events) and remembers the faster one for SPK_FLAG_AUTO_TRACER until the next spk_cuda_upload_scene. The
+/* Times 8 samples per pixel of the current scene and camera with the megakernel and with the wavefront tracer
+ * (CUDA events; the megakernel in its phased and its two material-sorted forms) and remembers the fastest for SPK_FLAG_AUTO_TRACER until the next spk_cuda_upload_scene. The
  * accumulator must be empty (it is used as scratch and cleared again). *wavefront_out: 0 megakernel, 1 wavefront;
  * ms_out[2]: the two times (may be NULL). */
 int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavefront_out, float *ms_out);
+/* What was chosen: *wavefront_out -1 not measured yet / 0 megakernel / 1 wavefront; *megakernel_form_out the form of the
+ * megakernel in use (831 phased, 1162 / 1084 sorted by material class with 16x2 / 8x4 warps x CTAs per SM). */
+int spk_cuda_tracer_choice(SpkContext *ctx, int32_t *wavefront_out, uint32_t *megakernel_form_out);
 /* ToneMappingPass + readback (CPURenderer.cpp:554-576; Renderer.cpp:108-180). `total_samples` is the
  * number of samples summed in the accumulator (all ranks, after the reduce) for SPK_ACCUM_SUM. */
 int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, void *host_out, size_t host_bytes);

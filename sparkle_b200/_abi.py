@@ -105,6 +105,7 @@ CUDA_SYMBOLS = {
     "spk_cuda_reset_accumulation": (C.c_int, [CtxP]),
     "spk_cuda_render": (C.c_int, [CtxP, C.POINTER(RenderParams)]),
     "spk_cuda_resolve": (C.c_int, [CtxP, u32, u32, C.c_void_p, C.c_size_t]),
+    "spk_cuda_tracer_choice": (C.c_int, [CtxP, C.POINTER(C.c_int32), C.POINTER(u32)]),
     "spk_cuda_choose_tracer": (C.c_int, [CtxP, u32, C.POINTER(u32), C.POINTER(C.c_float)]),
     "spk_cuda_accum_device_ptr": (C.c_int, [CtxP, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "spk_cuda_accum_sample_count": (C.c_int, [CtxP, u32p]),

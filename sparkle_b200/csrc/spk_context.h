@@ -49,6 +49,7 @@ struct SpkContext
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
     void *wf_block = nullptr;
     uint32_t wf_slots = 0;
+    int mega_variant = 1162; // megakernel form (SPK_RENDER_PHASED code) spk_cuda_choose_tracer measured fastest
     int tracer_choice = -1; // -1 not measured for this scene, 0 megakernel, 1 wavefront (spk_cuda_choose_tracer)
 };
 

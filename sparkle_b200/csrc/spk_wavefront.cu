@@ -184,26 +184,6 @@ __global__ void __launch_bounds__(kExtendWarps * 32)
     }
 }
 
-// material class of a traced slot: what the warp should be sorted by
-__device__ __forceinline__ uint32_t shade_class(const DScene &sc, uint32_t inst)
-{
-    if (inst == SPK_INVALID_ID)
-    {
-        return 0u;
-    }
-    const DInstance *__restrict__ in = sc.instances + inst;
-    const DMaterial &m = sc.materials[__ldg(&in->material)];
-    uint32_t key = 1u;
-    key += __ldg(&in->kind) == 1u ? 0u : 1u;              // sphere / mesh
-    key += __ldg(&m.type) == 1u ? 2u : 0u;                // pbr / dielectric
-    bool tex = (__ldg(&m.base_color_tex) & __ldg(&m.metallic_roughness_tex) & __ldg(&m.normal_tex) &
-                __ldg(&m.emissive_tex)) != SPK_INVALID_ID; // any texture bound
-    key += tex ? 4u : 0u;
-    bool emissive = __ldg(&m.emissive[0]) != 0.f || __ldg(&m.emissive[1]) != 0.f || __ldg(&m.emissive[2]) != 0.f;
-    key += emissive ? 8u : 0u;
-    return key; // 0..16
-}
-
 // ---- shade: SamplePixel's loop body after Intersect (CPURenderer.cpp:259-369) for every traced slot
 __global__ void __launch_bounds__(kShadeThreads)
     wf_shade_kernel(const DScene sc, const WfArgs a, WfState st, uint32_t cur, float4 *__restrict__ accum)

@@ -88,6 +88,11 @@ class CudaContext:
         A.check(self.lib.spk_cuda_choose_tracer(self.handle, max_bounce, C.byref(w), ms))
         return bool(w.value), (ms[0], ms[1])
 
+    def tracer_choice(self):
+        w, form = C.c_int32(-1), C.c_uint32(0)
+        A.check(self.lib.spk_cuda_tracer_choice(self.handle, C.byref(w), C.byref(form)))
+        return w.value, form.value
+
     def stats(self):
         s = A.Stats()
         A.check(self.lib.spk_cuda_get_stats(self.handle, C.byref(s)))

@@ -34,7 +34,7 @@ def test_header_symbols_are_exported():
 
 def test_host_library_symbols():
     lib = A.host_lib()
-    for hdr in ("bvh_builder.h", "cuda_renderer.h"):
+    for hdr in ("bvh_builder.h", "cuda_renderer.h", "gltf_loader.h"):
         path = os.path.join(ROOT, "sparkle_b200", "host", hdr)
         if not os.path.exists(path):
             continue
