@@ -1,0 +1,133 @@
+"""Parity at BASELINE.json's full sizes, through properties that do not need the oracle to run the whole workload:
+  C3  soup-1M, 64 M incoherent rays: the persistent warp-scheduled kernel and the thread-per-ray kernel (two different
+      traversal loops) agree bit for bit on every ray; culled == exact traversal; a random subset equals the oracle.
+  C2  TestScene at 1920x1080: a sample range split over launches gives the same bits, the megakernel forms agree bit for
+      bit, the wavefront tracer agrees to summation order, and the image equals the oracle's at equal spp (<= 1e-3).
+  C4  city-10M (16 x 62,500 triangles, 160 instances) at 3840x2160: megakernel == wavefront to summation order, closest
+      hits of a ray batch bit-exact against the oracle on the full scene."""
+import numpy as np
+import pytest
+
+from sparkle_b200 import _abi as A
+from sparkle_b200 import geometry, scenes
+from sparkle_b200.device import HIT_DTYPE, CudaContext
+from sparkle_b200.scene import orbit_camera
+
+pytestmark = pytest.mark.gpu
+
+
+def test_c3_64m_rays_two_kernels_agree(oracle):
+    torch = pytest.importorskip("torch")
+    n = 64 << 20
+    sb, _ = scenes.soup(1_000_000)
+    desc = sb.finalize()
+    ctx = CudaContext(64, 64)
+    ctx.upload_scene(desc)
+    g = torch.Generator(device="cuda").manual_seed(2)
+    rays = torch.empty((n, 8), dtype=torch.float32, device="cuda")
+    rays[:, 0:3] = torch.rand((n, 3), generator=g, device="cuda") * 3.0 - 1.5
+    d = torch.randn((n, 3), generator=g, device="cuda")
+    rays[:, 4:7] = d / d.norm(dim=1, keepdim=True)
+    rays[:, 3] = 0
+    rays[:, 7] = 0
+    del d
+    hits_a = torch.empty((n, 5), dtype=torch.float32, device="cuda")
+    hits_b = torch.empty((n, 5), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.trace_closest_device(rays.data_ptr(), n, hits_a.data_ptr(), 0)
+    ctx.synchronize()
+    ms = ctx.stats()["last_ms"]
+    ctx.trace_closest_device(rays.data_ptr(), n, hits_b.data_ptr(), A.FLAG_THREAD_PER_RAY)
+    ctx.synchronize()
+    assert torch.equal(hits_a.view(torch.int32), hits_b.view(torch.int32)), "persistent vs thread-per-ray kernels differ"
+    hit_frac = float((hits_a[:, 3].view(torch.int32) != -1).float().mean())
+    assert 0.2 < hit_frac < 0.999
+    print(f"C3: 64M rays in {ms:.1f} ms = {n / ms / 1e3:.0f} Mrays/s, {hit_frac:.3f} hit")
+    # culled == exact on the first 4 M rays
+    m = 4 << 20
+    ctx.trace_closest_device(rays.data_ptr(), m, hits_b.data_ptr(), A.FLAG_EXACT_TRAVERSAL)
+    ctx.synchronize()
+    assert torch.equal(hits_a[:m].view(torch.int32), hits_b[:m].view(torch.int32)), "culled vs exact traversal differ"
+    # a random subset against the oracle, bit for bit
+    idx = torch.randint(0, n, (100_000,), generator=g, device="cuda")
+    sub_rays = np.ascontiguousarray(rays[idx].cpu().numpy())
+    sub_hits = np.ascontiguousarray(hits_a[idx].cpu().numpy()).view(np.uint32)
+    ref, _ = oracle.trace_closest(desc, sub_rays)
+    assert np.array_equal(sub_hits[:, 0], ref["t"].view(np.uint32))
+    assert np.array_equal(sub_hits[:, 3], ref["prim"]) and np.array_equal(sub_hits[:, 4], ref["face"])
+    ctx.close()
+
+
+def test_c2_full_resolution(oracle, monkeypatch):
+    w, h, spp = 1920, 1080, 4
+    sb, camkw = scenes.testscene()
+    desc = sb.finalize()
+    cam = orbit_camera(w, h, **camkw)
+    ctx = CudaContext(w, h)
+    ctx.upload_scene(desc)
+    ctx.set_camera(cam)
+    ctx.render(0, spp)
+    whole = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    ctx.reset_accumulation()
+    ctx.render(0, 1)
+    ctx.render(1, spp - 1)
+    assert np.array_equal(ctx.resolve(A.RESOLVE_LINEAR_F32), whole)  # sample split: same order of additions
+    ctx.reset_accumulation()
+    ctx.render(0, spp, flags=A.FLAG_WAVEFRONT)
+    wave = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    assert np.allclose(wave, whole, rtol=2e-6, atol=1e-6)
+    ref, _ = oracle.render(desc, cam, w, h, 0, spp, threads=15)
+    ref = ref / spp
+    rel = np.abs(whole[..., :3] - ref[..., :3]).sum(-1) / np.maximum(ref[..., :3].sum(-1), 1e-3)
+    mse = float(np.mean((whole[..., :3].astype(np.float64) - ref[..., :3]) ** 2))
+    psnr = 10 * np.log10(max(ref[..., :3].max(), 1e-6) ** 2 / max(mse, 1e-30))
+    print(f"C2 1920x1080 {spp} spp: mean rel err {rel.mean():.2e}, PSNR {psnr:.1f} dB, pixels > 1e-4: {(rel > 1e-4).mean():.2e}")
+    assert rel.mean() <= 1e-3 and psnr > 40
+    ctx.close()
+
+
+def test_c2_megakernel_forms_agree():
+    """phased, sorted 16x2 and sorted 8x4 are the same arithmetic in the same order (SPK_RENDER_PHASED is read once per
+    process, so the forms are compared through spk_cuda_choose_tracer's candidates on one context)"""
+    w, h = 640, 360
+    sb, camkw = scenes.room(num_objects=20, tex=64)
+    ctx = CudaContext(w, h)
+    ctx.upload_scene(sb.finalize())
+    ctx.set_camera(orbit_camera(w, h, **camkw))
+    ctx.render(0, 2, max_bounce=32)
+    before = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    ctx.reset_accumulation()
+    wavefront, ms = ctx.choose_tracer(32)
+    _, form = ctx.tracer_choice()
+    assert form in (831, 1162, 1084) and ms[0] > 0 and ms[1] > 0
+    ctx.render(0, 2, max_bounce=32)  # now with the chosen form
+    assert np.array_equal(ctx.resolve(A.RESOLVE_LINEAR_F32), before)
+    ctx.close()
+
+
+def test_c4_city_10m_at_4k(oracle):
+    w, h = 3840, 2160
+    sb, camkw = scenes.city()
+    desc = sb.finalize()
+    assert sum(sb.meshes[p["mesh"]].num_faces for p in sb.prims) > 9_900_000
+    ctx = CudaContext(w, h)
+    ctx.upload_scene(desc)
+    ctx.set_camera(orbit_camera(w, h, **camkw))
+    ctx.render(0, 1)
+    mega = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    st_m = ctx.stats()
+    ctx.reset_accumulation()
+    ctx.reset_stats()
+    ctx.render(0, 1, flags=A.FLAG_WAVEFRONT)
+    wave = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    st_w = ctx.stats()
+    assert np.array_equal(wave, mega)  # one sample per pixel: nothing to reorder
+    assert st_w["rays"] == st_m["rays"] and st_w["paths"] == w * h
+    rays = geometry.random_rays(200_000, seed=4, extent=40.0)
+    rays[:, 2] = np.abs(rays[:, 2]) * 0.2 + 0.1
+    ref, _ = oracle.trace_closest(desc, rays)
+    gpu = ctx.trace_closest(rays)
+    assert np.array_equal(gpu["prim"], ref["prim"]) and np.array_equal(gpu["face"], ref["face"])
+    assert np.array_equal(gpu["t"].view(np.uint32), ref["t"].view(np.uint32))
+    assert (ref["prim"] != A.INVALID_ID).mean() > 0.3
+    ctx.close()
