@@ -330,6 +330,105 @@ def run_cuda(args):
         dist.destroy_process_group()
 
 
+def run_trace(args):
+    """--workload c3 (BASELINE.json configs[2]): soup-1M, 64 M incoherent rays, closest hit only. One step = the whole
+    batch; N ranks take contiguous slices, no collective. value: device-resident rays and hits; e2e: host buffers
+    through spk_cuda_trace_closest on a 16 M-ray slice of the batch (stated in config)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from sparkle_b200 import _abi as A
+    from sparkle_b200 import multi_gpu, scenes
+    from sparkle_b200.device import CudaContext
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the cuda pipeline has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    total = 64 << 20
+    begin, end = multi_gpu.ray_slice(total, rank, world)
+    n = end - begin
+    sb, _ = scenes.soup(1_000_000)
+    desc = sb.finalize()
+    ctx = CudaContext(64, 64, device=local)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    ctx.upload_scene(desc)
+    g = torch.Generator(device="cuda").manual_seed(2 + rank)
+    rays = torch.zeros((n, 8), dtype=torch.float32, device="cuda")
+    rays[:, 0:3] = torch.rand((n, 3), generator=g, device="cuda") * 3.0 - 1.5
+    d = torch.randn((n, 3), generator=g, device="cuda")
+    rays[:, 4:7] = d / d.norm(dim=1, keepdim=True)
+    del d
+    hits = torch.empty((n, 5), dtype=torch.float32, device="cuda")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for k in range(steps):
+            ev[k][0].record()
+            fn()
+            ev[k][1].record()
+        barrier()
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ctx.reset_stats()
+    cn = min(n, 4 << 20)
+    ctx.trace_closest_device(rays.data_ptr(), cn, hits.data_ptr(), A.FLAG_COUNTERS)
+    cst = ctx.stats()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total = timed(lambda: ctx.trace_closest_device(rays.data_ptr(), n, hits.data_ptr(), 0), args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    en = min(n, (16 << 20) // world)
+    h_rays = rays[:en].cpu().pin_memory()  # pinned host buffers, as the contract asks
+    h_hits = torch.empty((en, 5), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        A.check(ctx.lib.spk_cuda_trace_closest(ctx.handle, h_rays.data_ptr(), en, h_hits.data_ptr(), 0))
+
+    e2e_steps = max(1, min(args.steps, 3))
+    ms_e2e = timed(e2e_step, e2e_steps, 1)
+    if rank == 0:
+        peak, peak_src = peaks()
+        nv, tt = cst["node_visits"] / cn, cst["tri_tests"] / cn
+        bytes_ray = 32 + 20 + 64 * nv + 48 * tt + 128 * cst["inst_visits"] / cn
+        kernel_ms = ms_total / args.steps
+        achieved = bytes_ray * n / (kernel_ms * 1e-3) / 1e9
+        line = {"metric": "Mrays/s", "value": total * args.steps / (ms_total * 1e-3) / 1e6, "unit": "Mrays/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": kernel_ms,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "soup-1M (1,000,000 triangles, one mesh), 64 Mi incoherent rays, closest hit only "
+                                       "(BASELINE.json configs[2])",
+                           "parallelism": f"ray-slice x{world}", "l2": "inputs larger than L2 (2.1 GB rays, 1.3 GB hits per step)",
+                           "e2e_sample": f"{en * world} rays through host buffers"},
+                "clocks": clocks,
+                "e2e": {"value": en * world * e2e_steps / (ms_e2e * 1e-3) / 1e6, "unit": "Mrays/s",
+                        "h2d_bytes_per_step": en * 32, "d2h_bytes_per_step": en * 20, "ms_per_step": ms_e2e / e2e_steps},
+                "gpu_launches": args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": peak_src,
+                             "kernel": "trace_persistent_kernel<CULL=true, VOTE=6>", "alg_bytes_per_ray": bytes_ray,
+                             "node_visits_per_ray": nv, "tri_tests_per_ray": tt}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -337,10 +436,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["c3"])
     ap.add_argument("--spp", type=int, default=0, help="bound the workload's spp (stated in config.workload)")
     ap.add_argument("--tracer", default="auto", choices=["auto", "megakernel", "wavefront"])
     args = ap.parse_args()
+    if args.workload == "c3":
+        args.warmup = max(args.warmup, 3)
+        if args.impl == "cuda":
+            return run_trace(args)
+        raise SystemExit("bench.py: --workload c3 has no reference arm here (tests compare it with the oracle)")
     select_workload(args)
     args.warmup = max(args.warmup, 3) if args.impl == "cuda" else args.warmup
     if args.impl == "reference":
