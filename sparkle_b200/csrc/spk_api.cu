@@ -9,7 +9,10 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <memory>
 #include <new>
+#include <thread>
 
 namespace spk
 {
@@ -54,6 +57,36 @@ uint32_t read_prim_id(const SpkBvhDesc &d, uint32_t k)
 }
 
 // structural checks the reference never makes (a malformed tree would overflow its SmallStack<Index,32>)
+// host-side flattening of a 1M-triangle scene on one thread was 110 ms of every end-to-end step: work items are spread
+// over up to 8 host threads (errors are reported by index, the message is set by the caller's thread)
+template <typename Fn> void parallel_for(size_t n, Fn &&fn)
+{
+    unsigned workers = std::min<size_t>(std::min(8u, std::max(1u, std::thread::hardware_concurrency())), n);
+    if (workers <= 1)
+    {
+        for (size_t i = 0; i < n; i++)
+        {
+            fn(i);
+        }
+        return;
+    }
+    std::atomic<size_t> next{0};
+    std::vector<std::thread> pool;
+    for (unsigned w = 0; w < workers; w++)
+    {
+        pool.emplace_back([&] {
+            for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1))
+            {
+                fn(i);
+            }
+        });
+    }
+    for (auto &t : pool)
+    {
+        t.join();
+    }
+}
+
 int validate_bvh(const SpkBvhDesc &d, uint32_t expected_prims, const char *what)
 {
     if (!d.nodes || d.num_nodes == 0 || (d.node_stride != 28 && d.node_stride != 32) || !d.prim_ids ||
@@ -327,26 +360,37 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         return invalid("spk_cuda_upload_scene: null table");
     }
     uint64_t total_pairs = 0, total_tris = 0;
-    for (uint32_t m = 0; m < s->num_meshes; m++)
-    {
+    std::vector<int> mesh_status(s->num_meshes, 0); // 0 ok, 1 missing arrays, 2 index out of range, 3 malformed BLAS
+    parallel_for(s->num_meshes, [&](size_t m) {
         const SpkMeshDesc &md = s->meshes[m];
         if (!md.vertices || !md.normals || !md.tangents || !md.indices || md.num_faces == 0 || md.num_vertices == 0)
         {
-            return invalid("spk_cuda_upload_scene: mesh needs vertices, normals, tangents, indices");
+            mesh_status[m] = 1;
+            return;
         }
         for (size_t k = 0; k < size_t(md.num_faces) * 3; k++)
         {
             if (md.indices[k] >= md.num_vertices)
             {
-                return invalid("spk_cuda_upload_scene: vertex index out of range");
+                mesh_status[m] = 2;
+                return;
             }
         }
-        if ((rc = validate_bvh(md.blas, md.num_faces, "spk_cuda_upload_scene: malformed BLAS")) != SPK_OK)
+        if (validate_bvh(md.blas, md.num_faces, "") != SPK_OK)
         {
-            return rc;
+            mesh_status[m] = 3;
         }
-        total_pairs += (md.blas.num_nodes - 1) / 2;
-        total_tris += md.num_faces;
+    });
+    for (uint32_t m = 0; m < s->num_meshes; m++)
+    {
+        if (mesh_status[m] != 0)
+        {
+            return invalid(mesh_status[m] == 1   ? "spk_cuda_upload_scene: mesh needs vertices, normals, tangents, indices"
+                           : mesh_status[m] == 2 ? "spk_cuda_upload_scene: vertex index out of range"
+                                                 : "spk_cuda_upload_scene: malformed BLAS");
+        }
+        total_pairs += (s->meshes[m].blas.num_nodes - 1) / 2;
+        total_tris += s->meshes[m].num_faces;
     }
     for (uint32_t p = 0; p < s->num_primitives; p++)
     {
@@ -387,23 +431,58 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     }
 
     // ---- flatten BLAS pairs + triangles (leaf order) ----
-    std::vector<float> pairs(size_t(total_pairs) * 16);
-    std::vector<float> tris(size_t(total_tris) * 12);
+    // uninitialised on purpose: every word is written below, and zero-filling 80 MB first costs tens of ms of page faults
+    // on one thread (the parallel writers below take the faults instead). One spare pair so an all-leaf scene still has
+    // a valid (never dereferenced) pointer.
+    const size_t pair_floats = size_t(total_pairs) * 16 + 16, tri_floats = size_t(total_tris) * 12;
+    std::unique_ptr<float[]> pairs_buf(new (std::nothrow) float[pair_floats]);
+    std::unique_ptr<float[]> tris_buf(new (std::nothrow) float[tri_floats ? tri_floats : 1]);
+    if (!pairs_buf || !tris_buf)
+    {
+        return SPK_ERR_OUT_OF_MEMORY;
+    }
+    memset(pairs_buf.get() + size_t(total_pairs) * 16, 0, 64);
+    struct
+    {
+        float *p;
+        float *data() const { return p; }
+    } pairs{pairs_buf.get()}, tris{tris_buf.get()};
     std::vector<DMesh> dmeshes(s->num_meshes);
     ctx->mesh_root_word.assign(s->num_meshes, 0);
     uint32_t pair_base = 0, tri_base = 0;
+    // work items: one flatten_pairs per mesh, and the triangle records in chunks of 64 Ki faces
+    struct Item
+    {
+        uint32_t mesh, pair_base, tri_base, begin, end; // begin == end: the pair item
+    };
+    std::vector<Item> items;
     for (uint32_t m = 0; m < s->num_meshes; m++)
     {
         const SpkMeshDesc &md = s->meshes[m];
-        flatten_pairs(md.blas, pair_base, tri_base, pairs.data() + size_t(pair_base) * 16);
-        ctx->mesh_root_word[m] = root_word(md.blas, pair_base, tri_base);
-        for (uint32_t k = 0; k < md.num_faces; k++)
+        items.push_back(Item{m, pair_base, tri_base, 0, 0});
+        for (uint32_t b = 0; b < md.num_faces; b += 65536u)
+        {
+            items.push_back(Item{m, pair_base, tri_base, b, std::min(md.num_faces, b + 65536u)});
+        }
+        pair_base += (md.blas.num_nodes - 1) / 2;
+        tri_base += md.num_faces;
+    }
+    parallel_for(items.size(), [&](size_t w) {
+        const Item &it = items[w];
+        const SpkMeshDesc &md = s->meshes[it.mesh];
+        if (it.begin == it.end)
+        {
+            flatten_pairs(md.blas, it.pair_base, it.tri_base, pairs.data() + size_t(it.pair_base) * 16);
+            ctx->mesh_root_word[it.mesh] = root_word(md.blas, it.pair_base, it.tri_base);
+            return;
+        }
+        for (uint32_t k = it.begin; k < it.end; k++)
         {
             uint32_t face = read_prim_id(md.blas, k);
             const float *v0 = md.vertices + size_t(md.indices[size_t(face) * 3 + 0]) * 3;
             const float *v1 = md.vertices + size_t(md.indices[size_t(face) * 3 + 1]) * 3;
             const float *v2 = md.vertices + size_t(md.indices[size_t(face) * 3 + 2]) * 3;
-            float *o = tris.data() + size_t(tri_base + k) * 12;
+            float *o = tris.data() + size_t(it.tri_base + k) * 12;
             // Triangle::Set (MeshRenderProxy.cpp:80-86): p0 = v0, e1 = v1 - v0, e2 = v2 - v0
             for (int a = 0; a < 3; a++)
             {
@@ -415,6 +494,12 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
             o[7] = 0.f;
             o[11] = 0.f;
         }
+    });
+    pair_base = 0;
+    tri_base = 0;
+    for (uint32_t m = 0; m < s->num_meshes; m++)
+    {
+        const SpkMeshDesc &md = s->meshes[m];
         float *dn = nullptr, *dt = nullptr, *du = nullptr;
         uint32_t *di = nullptr;
         if ((rc = upload(ctx, md.normals, size_t(md.num_vertices) * 3, &dn)) != SPK_OK ||
@@ -453,10 +538,8 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     float4 *d_pairs = nullptr, *d_tris = nullptr;
     DInstance *d_inst = nullptr;
     DMesh *d_meshes = nullptr;
-    // one spare pair so an all-leaf scene still has a valid (never dereferenced) pointer
-    pairs.resize(pairs.size() + 16, 0.f);
-    if ((rc = upload(ctx, reinterpret_cast<const float4 *>(pairs.data()), pairs.size() / 4, &d_pairs)) != SPK_OK ||
-        (rc = upload(ctx, reinterpret_cast<const float4 *>(tris.data()), tris.size() / 4, &d_tris)) != SPK_OK ||
+    if ((rc = upload(ctx, reinterpret_cast<const float4 *>(pairs.data()), pair_floats / 4, &d_pairs)) != SPK_OK ||
+        (rc = upload(ctx, reinterpret_cast<const float4 *>(tris.data()), tri_floats / 4, &d_tris)) != SPK_OK ||
         (rc = upload(ctx, instances.data(), instances.size(), &d_inst)) != SPK_OK ||
         (rc = upload(ctx, dmeshes.data(), dmeshes.size(), &d_meshes)) != SPK_OK)
     {

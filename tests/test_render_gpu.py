@@ -162,11 +162,15 @@ def test_wavefront_equals_megakernel(name, bounce, spp, oracle, monkeypatch):
 
 def test_spatial_denoise(oracle):
     """a15 (SPK_FLAG_SPATIAL_DENOISE): g-buffer sample, 8-neighbour fill of invalid pixels, running average"""
+    import oracle_lib as O
+    # the port: the reference's scatter is a race between row workers once its pool has more than one (the pool is
+    # created once per process); the port is the one-worker order, pinned against the reference in test_oracle_cpu.py
+    orc = O.Oracle("port")
     w, h = 96, 64
     sb, desc, cam = build("room", w, h)
-    ref, cum = oracle.render(desc, cam, w, h, 0, 3, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1,
-                             flags=A.FLAG_SPATIAL_DENOISE)
-    plain, _ = oracle.render(desc, cam, w, h, 0, 3, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1)
+    ref, cum = orc.render(desc, cam, w, h, 0, 3, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1,
+                          flags=A.FLAG_SPATIAL_DENOISE)
+    plain, _ = orc.render(desc, cam, w, h, 0, 3, max_bounce=32, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=1)
     ctx = CudaContext(w, h)
     ctx.upload_scene(desc)
     ctx.set_camera(cam)
