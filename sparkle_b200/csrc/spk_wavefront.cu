@@ -460,7 +460,7 @@ int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *p)
     a.max_bounce = p->max_bounce;
     a.output_limit = p->output_limit;
     const unsigned long long total = (unsigned long long)a.width * a.height * p->sample_count;
-    uint32_t slots = env_u32("SPK_WF_SLOTS", 1u << 20);
+    uint32_t slots = env_u32("SPK_WF_SLOTS", 1u << 24); // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
     if (slots > total)
     {
         slots = uint32_t(total);
