@@ -231,7 +231,8 @@ void free_scene(SpkContext *ctx)
     ctx->d_instances = nullptr;
 }
 
-void fill_instance(DInstance &di, const SpkPrimitiveDesc &pd, uint32_t prim, const std::vector<uint32_t> &mesh_root)
+void fill_instance(DInstance &di, const SpkPrimitiveDesc &pd, uint32_t prim, const std::vector<uint32_t> &mesh_root,
+                   const std::vector<uint32_t> &material_class)
 {
     memset(&di, 0, sizeof(di));
     memcpy(di.inv, pd.inv, 48);
@@ -242,6 +243,10 @@ void fill_instance(DInstance &di, const SpkPrimitiveDesc &pd, uint32_t prim, con
     di.material = pd.material;
     di.mesh = pd.kind == SPK_PRIM_MESH ? pd.mesh : SPK_INVALID_ID;
     di.root = pd.kind == SPK_PRIM_MESH ? mesh_root[pd.mesh] : 0u;
+    // shade_class (spk_shade.cuh): 1 + mesh + 2 dielectric + 4 textured + 8 emissive, precomputed so the shading sort needs
+    // one load per segment instead of instance -> material
+    di.shade_class = 1u + (pd.kind == SPK_PRIM_MESH ? 1u : 0u) +
+                     (pd.material < material_class.size() ? material_class[pd.material] : 0u);
 }
 } // namespace
 } // namespace spk
@@ -520,6 +525,14 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     ctx->num_blas_pairs = pair_base;
     ctx->tlas_pair_base = pair_base;
 
+    ctx->material_class.assign(s->num_materials, 0u);
+    for (uint32_t m = 0; m < s->num_materials; m++)
+    {
+        const SpkMaterialDesc &md = s->materials[m];
+        const bool textured = (md.base_color_tex & md.metallic_roughness_tex & md.normal_tex & md.emissive_tex) != SPK_INVALID_ID;
+        const bool emissive = md.emissive[0] != 0.f || md.emissive[1] != 0.f || md.emissive[2] != 0.f;
+        ctx->material_class[m] = (md.type == SPK_MAT_DIELECTRIC ? 2u : 0u) + (textured ? 4u : 0u) + (emissive ? 8u : 0u);
+    }
     // ---- TLAS pairs + instances in TLAS leaf order (SceneRenderProxy.cpp:59-68) ----
     std::vector<DInstance> instances(s->num_primitives);
     if (s->num_primitives)
@@ -529,7 +542,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         for (uint32_t k = 0; k < s->num_primitives; k++)
         {
             uint32_t prim = read_prim_id(s->tlas, k);
-            fill_instance(instances[k], s->primitives[prim], prim, ctx->mesh_root_word);
+            fill_instance(instances[k], s->primitives[prim], prim, ctx->mesh_root_word, ctx->material_class);
         }
     }
     ctx->pair_capacity = uint32_t(total_pairs);
@@ -639,7 +652,7 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
     for (uint32_t k = 0; k < num_primitives; k++)
     {
         uint32_t prim = read_prim_id(*tlas, k);
-        fill_instance(instances[k], primitives[prim], prim, ctx->mesh_root_word);
+        fill_instance(instances[k], primitives[prim], prim, ctx->mesh_root_word, ctx->material_class);
     }
     if (tlas_pairs)
     {

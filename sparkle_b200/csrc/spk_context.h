@@ -19,6 +19,7 @@ struct SpkContext
     std::vector<void *> scene_allocs; // everything the current scene owns on the device
     // kept for spk_cuda_update_instances
     std::vector<uint32_t> mesh_root_word;
+    std::vector<uint32_t> material_class; // per material: 2 dielectric + 4 textured + 8 emissive (DInstance::shade_class)
     uint32_t tlas_pair_base = 0;
     uint32_t num_blas_pairs = 0;
     uint32_t pair_capacity = 0;

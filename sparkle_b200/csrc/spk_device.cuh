@@ -43,7 +43,8 @@ struct __align__(16) DInstance
     uint32_t prim; // primitive index in SceneRenderProxy::primitives_ registration order
     uint32_t material;
     uint32_t mesh;
-    uint32_t pad[2];
+    uint32_t shade_class; // 1 + mesh + 2 dielectric + 4 textured + 8 emissive: the key segments are sorted by before shading
+    uint32_t pad;
 };
 static_assert(sizeof(DInstance) == 128, "instance record");
 

@@ -508,21 +508,8 @@ __device__ __forceinline__ V3 sample_surface(const DScene &sc, Rng &rng, const S
 // material class of a traced segment: the key warps are regrouped by before shading (wf_shade, render_sorted_kernel)
 __device__ __forceinline__ uint32_t shade_class(const DScene &sc, uint32_t inst)
 {
-    if (inst == SPK_INVALID_ID)
-    {
-        return 0u;
-    }
-    const DInstance *__restrict__ in = sc.instances + inst;
-    const DMaterial &m = sc.materials[__ldg(&in->material)];
-    uint32_t key = 1u;
-    key += __ldg(&in->kind) == 1u ? 0u : 1u;              // sphere / mesh
-    key += __ldg(&m.type) == 1u ? 2u : 0u;                // pbr / dielectric
-    bool tex = (__ldg(&m.base_color_tex) & __ldg(&m.metallic_roughness_tex) & __ldg(&m.normal_tex) &
-                __ldg(&m.emissive_tex)) != SPK_INVALID_ID; // any texture bound
-    key += tex ? 4u : 0u;
-    bool emissive = __ldg(&m.emissive[0]) != 0.f || __ldg(&m.emissive[1]) != 0.f || __ldg(&m.emissive[2]) != 0.f;
-    key += emissive ? 8u : 0u;
-    return key; // 0..16
+    // 0 miss; else 1 + mesh + 2 dielectric + 4 textured + 8 emissive, precomputed per instance at upload (spk_api.cu)
+    return inst == SPK_INVALID_ID ? 0u : __ldg(&sc.instances[inst].shade_class); // 0..16
 }
 
 // ---- SkyRenderProxy::Evaluate ----
