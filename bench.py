@@ -64,6 +64,17 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def recorded_traffic(key, **match):
+    """dram bytes per launch of the dominant kernel from the committed ncu pass (profiles/r1_dram_traffic.json), or None
+    when this run's launch is not the one that was captured"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_dram_traffic.json")) as f:
+            rec = json.load(f)[key]
+    except Exception:
+        return None
+    return rec["dram_bytes"] if all(rec.get(k) == v for k, v in match.items()) else None
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons DURING the timed region"""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -294,6 +305,9 @@ def run_cuda(args):
     alg_bytes = (64 * cst["node_visits"] + 48 * cst["tri_tests"] + 128 * cst["inst_visits"] + 16 * cst["sphere_tests"]) * scale \
         + 2 * 16 * WIDTH * HEIGHT
     kernel_ms = ms_total / args.steps  # the render kernel is the step at N=1 (memset + 1 launch)
+    traffic = None
+    if world == 1 and not use_wavefront and args.workload == "c2":
+        traffic = recorded_traffic("c2", form=ctx.tracer_choice()[1], width=WIDTH, height=HEIGHT, spp_per_launch=SPP)
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
     rays_total = st["rays"] / max(1, args.steps + args.warmup) * world
     line = {
@@ -310,7 +324,7 @@ def run_cuda(args):
                 "ms_per_step": ms_e2e / e2e_steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": ("wf_extend_kernel<CULL=true> (+ wf_shade/regen/advance; achieved is over the whole step)"
+                     "traffic": traffic, "peak_source": peak_src, "kernel": ("wf_extend_kernel<CULL=true> (+ wf_shade/regen/advance; achieved is over the whole step)"
                                 if use_wavefront else {831: "render_phased_kernel<CULL=true, 8 warps x 3 CTAs/SM>",
                                       1162: "render_sorted_kernel<CULL=true, 16 warps x 2 CTAs/SM>",
                                       1084: "render_sorted_kernel<CULL=true, 8 warps x 4 CTAs/SM>"}.get(
@@ -421,7 +435,8 @@ def run_trace(args):
                         "h2d_bytes_per_step": en * 32, "d2h_bytes_per_step": en * 20, "ms_per_step": ms_e2e / e2e_steps},
                 "gpu_launches": args.steps,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": peak_src,
+                             "traffic": recorded_traffic("c3", rays_per_launch=n) if world == 1 else None,
+                             "peak_source": peak_src,
                              "kernel": "trace_persistent_kernel<CULL=true, VOTE=6>", "alg_bytes_per_ray": bytes_ray,
                              "node_visits_per_ray": nv, "tri_tests_per_ray": tt}}
         print(json.dumps(line), flush=True)

@@ -3,6 +3,7 @@
 #include "../../include/spk_cuda.h"
 #include "spk_device.cuh"
 
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <string>
 #include <vector>
@@ -65,6 +66,20 @@ int cuda_fail(cudaError_t e, const char *what);
         if (e__ != cudaSuccess)                                                                                        \
             return spk::cuda_fail(e__, #expr);                                                                         \
     } while (0)
+
+// Shared memory and L1 split one 256 KB array per SM. Asks for the smallest carve-out that still holds `ctas` resident
+// CTAs of `bytes_per_cta` (+1 KB the driver reserves per CTA), so that the rest serves the BVH as L1: the default
+// heuristic leaves the traversal kernels ~32 KB less L1 than they can have (measured: DESIGN.md 4.2).
+template <class Kernel> cudaError_t prefer_small_carveout(Kernel kernel, size_t bytes_per_cta, int ctas)
+{
+    const size_t pool = 228 * 1024;
+    int pct = int((size_t(ctas) * (bytes_per_cta + 1024) * 100 + pool - 1) / pool);
+    if (const char *e = getenv("SPK_CARVEOUT"))
+        pct = atoi(e);
+    if (pct < 0)
+        return cudaSuccess; // SPK_CARVEOUT=-1: the driver's default
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
+}
 
 // kernels (spk_trace.cu / spk_render.cu)
 int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags);

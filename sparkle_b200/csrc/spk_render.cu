@@ -682,7 +682,9 @@ template <int W, int B> cudaError_t sorted_allow_smem()
         const int bytes = (int)sorted_smem_bytes<W>();
 #define SPK_ALLOW(C, N)                                                                                                \
     if (e == cudaSuccess)                                                                                              \
-        e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);    \
+    if (e == cudaSuccess)                                                                                              \
+        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B>, bytes + (W * 32 + 32) * 4, B);
         SPK_ALLOW(true, false)
         SPK_ALLOW(false, false)
         SPK_ALLOW(true, true)

@@ -127,6 +127,7 @@ static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, fl
         SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, 0));
         SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
         blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
+        SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32, blocks_per_sm));
     }
     uint64_t want = (n + kPersistWarps * 32 - 1) / (kPersistWarps * 32);
     uint64_t resident = uint64_t(blocks_per_sm) * sms; // one wave of persistent CTAs: a multiple of the SM count

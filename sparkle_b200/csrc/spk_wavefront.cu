@@ -401,6 +401,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t 
         SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, extend, kExtendWarps * 32, 0));
         SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
         blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
+        SPK_CUDA_TRY(spk::prefer_small_carveout(extend, sizeof(uint32_t) * kExtendWarps * kLaneSmemWords * 32, blocks_per_sm));
     }
     const unsigned long long total = (unsigned long long)a.width * a.height * sample_count;
     const uint32_t slots = st.slots;
