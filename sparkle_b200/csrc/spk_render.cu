@@ -419,10 +419,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
         acc = accum[size_t(j) * a.width + i];
     }
     uint32_t stack[64];
-    uint32_t s = 0, bounce = 0;
+    uint32_t s = 0;
     bool live = in_image, need_path = true;
-    Rng rng;
-    V3 origin, dir, throughput;
+    // The path state (ray, throughput, rng, bounce) lives ONLY in this thread's shared-memory column between the
+    // phases: phase A writes a new path into it, phase B reads the ray, the shading thread of phase C updates it in
+    // place. Nothing of it stays in registers across the traversal, which is what used to spill (and the spill lines
+    // competed with the BVH for L1).
+    float *col = s_state + tid;
     for (;;)
     {
         // ---- phase A: next sample of this pixel
@@ -435,7 +438,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             else
             {
                 const uint32_t frame_seed = a.first_sample + s * a.sample_stride; // CPURenderer.cpp:442-443
-                rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+                Rng rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
                 float u = ((float)i + rng_unit(rng)) * pw;
                 float v = ((float)j + rng_unit(rng)) * ph;
                 float dx, dy;
@@ -448,11 +451,23 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                 const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
                 const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
                 const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
-                origin = cpos + (dx * cright + dy * cup);
+                const V3 origin = cpos + (dx * cright + dy * cup);
                 V3 target = lower_left + u * max_u + v * max_v;
-                dir = normalized(target - origin);
-                throughput = mk(1.f, 1.f, 1.f);
-                bounce = 0;
+                const V3 dir = normalized(target - origin);
+                col[0 * T] = origin.x;
+                col[1 * T] = origin.y;
+                col[2 * T] = origin.z;
+                col[3 * T] = dir.x;
+                col[4 * T] = dir.y;
+                col[5 * T] = dir.z;
+                col[6 * T] = 1.f; // throughput
+                col[7 * T] = 1.f;
+                col[8 * T] = 1.f;
+                col[9 * T] = __uint_as_float(rng.s0);
+                col[10 * T] = __uint_as_float(rng.s1);
+                col[11 * T] = __uint_as_float(rng.s2);
+                col[12 * T] = __uint_as_float(rng.s3);
+                col[18 * T] = __uint_as_float(0u); // bounce
                 need_path = false;
             }
         }
@@ -465,38 +480,24 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             break;
         }
         // ---- phase B: one path segment
-        float *col = s_state + tid;
         Hit hit;
         hit.t = 0.f;
         hit.u = 0.f;
         hit.v = 0.f;
         hit.inst = SPK_INVALID_ID;
         hit.face = SPK_INVALID_ID;
-        col[0 * T] = origin.x;
-        col[1 * T] = origin.y;
-        col[2 * T] = origin.z;
-        col[3 * T] = dir.x;
-        col[4 * T] = dir.y;
-        col[5 * T] = dir.z;
         if (live)
         {
+            const V3 origin = mk(col[0 * T], col[1 * T], col[2 * T]), dir = mk(col[3 * T], col[4 * T], col[5 * T]);
             trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
             rays++;
         }
-        // ---- phase C: park the segment, sort by class, shade the sorted one, hand the outcome back
-        col[6 * T] = throughput.x;
-        col[7 * T] = throughput.y;
-        col[8 * T] = throughput.z;
-        col[9 * T] = __uint_as_float(rng.s0);
-        col[10 * T] = __uint_as_float(rng.s1);
-        col[11 * T] = __uint_as_float(rng.s2);
-        col[12 * T] = __uint_as_float(rng.s3);
+        // ---- phase C: park the hit, sort by class, shade the sorted segment, hand the outcome back
         col[13 * T] = hit.t;
         col[14 * T] = hit.u;
         col[15 * T] = hit.v;
         col[16 * T] = __uint_as_float(hit.inst);
         col[17 * T] = __uint_as_float(hit.face);
-        col[18 * T] = __uint_as_float(bounce);
         const uint32_t key = live ? shade_class(sc, hit.inst) : 31u;
         const uint32_t pos = atomicAdd(&s_bin[key], 1u);
         __syncthreads();
@@ -634,17 +635,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                 s++;
                 need_path = true;
             }
-            else
-            {
-                origin = mk(col[0 * T], col[1 * T], col[2 * T]);
-                dir = mk(col[3 * T], col[4 * T], col[5 * T]);
-                throughput = mk(col[6 * T], col[7 * T], col[8 * T]);
-                rng.s0 = __float_as_uint(col[9 * T]);
-                rng.s1 = __float_as_uint(col[10 * T]);
-                rng.s2 = __float_as_uint(col[11 * T]);
-                rng.s3 = __float_as_uint(col[12 * T]);
-                bounce = __float_as_uint(col[18 * T]);
-            }
+            // else: the shading thread left the next segment in this column
         }
         // (the barrier at the top of the loop separates these reads from the next iteration's column writes)
     }
