@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
         const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
         float4 acc = GBUF ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(j) * a.width + i];
         V3 first_normal = mk(0.f, 0.f, 0.f);
-        uint32_t stack[64];
+        uint32_t stack[kThreadStack];
         for (uint32_t s = 0; s < a.sample_count; s++)
         {
             // CPURenderer.cpp:442-443, unsigned wrap
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     {
         acc = accum[size_t(j) * a.width + i];
     }
-    uint32_t stack[64];
+    uint32_t stack[kThreadStack];
     uint32_t s = 0, bounce = 0;
     bool live = in_image, need_path = true;
     Rng rng;
@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     {
         acc = accum[size_t(j) * a.width + i];
     }
-    uint32_t stack[64];
+    uint32_t stack[kThreadStack];
     uint32_t s = 0;
     bool live = in_image, need_path = true;
     // The path state (ray, throughput, rng, bounce) lives ONLY in this thread's shared-memory column between the

@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(kTraceThreads)
     if (i < n)
     {
         float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
-        uint32_t stack[64];
+        uint32_t stack[kThreadStack];
         Hit best;
         trace_closest<CULL, COUNT>(sc, mk(ro.x, ro.y, ro.z), mk(rd.x, rd.y, rd.z), best, stack, cnt);
         float *o = hits + 5 * i;

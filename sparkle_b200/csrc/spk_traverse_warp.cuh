@@ -125,7 +125,7 @@ __device__ __forceinline__ bool lane_pop(LaneState &s, LaneStack &stack)
     }
 }
 
-// one bvh::v2 inner step (identical to the loop body of traverse_tree); returns false when the ray is finished
+// one bvh::v2 inner step (the loop body of trace_closest); returns false when the ray is finished
 template <bool CULL, bool COUNT>
 __device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs, LaneState &s, LaneStack &stack,
                                                 TraceCounters &cnt)
