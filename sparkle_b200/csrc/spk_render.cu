@@ -385,7 +385,7 @@ need_path = false;
 // per-pixel arithmetic and the order samples are added are unchanged.
 template <int WARPS> constexpr size_t sorted_smem_bytes()
 {
-    return size_t(20 * WARPS * 32) * 4;
+    return size_t(23 * WARPS * 32) * 4;
 }
 
 // Measured and dropped: a CTA-local ray QUEUE for phase B (the 256 parked rays drained by the warps with
@@ -398,38 +398,33 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                          unsigned long long *__restrict__ counters)
 {
     constexpr int T = WARPS * 32;
-    constexpr int kWords = 20;
     extern __shared__ __align__(16) unsigned char s_dynamic[]; // sorted_smem_bytes<WARPS>()
     float *s_state = reinterpret_cast<float *>(s_dynamic);
-    __shared__ uint32_t s_bin[32];
-    __shared__ uint32_t s_sorted[T];
+    __shared__ uint32_t s_bin[2][32];
+    __shared__ uint32_t s_total;
+    __shared__ uint16_t s_sorted[T];
     const uint32_t tid = threadIdx.x;
     const uint32_t tiles_x = (a.width + kTileW - 1) / kTileW;
-    const uint32_t warp = blockIdx.x * WARPS + (tid >> 5);
     const uint32_t lane = tid & 31;
-    const uint32_t i = (warp % tiles_x) * kTileW + (lane & (kTileW - 1));
-    const uint32_t j = (warp / tiles_x) * kTileH + (lane / kTileW);
+    // column c of the CTA <-> pixel: a warp-sized run of columns is one 8x4 tile
+    auto pixel_of = [&](uint32_t c, uint32_t &pi, uint32_t &pj) {
+        const uint32_t w = blockIdx.x * WARPS + (c >> 5), l = c & 31u;
+        pi = (w % tiles_x) * kTileW + (l & (kTileW - 1));
+        pj = (w / tiles_x) * kTileH + (l / kTileW);
+    };
+    uint32_t i, j;
+    pixel_of(tid, i, j);
     const bool in_image = i < a.width && j < a.height;
     uint32_t rays = 0;
     TraceCounters cnt{0, 0, 0, 0};
     const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (in_image)
-    {
-        acc = accum[size_t(j) * a.width + i];
-    }
     uint32_t stack[kThreadStack];
-    uint32_t s = 0;
-    bool live;
-    // The path state (ray, throughput, rng, bounce) lives ONLY in this thread's shared-memory column between the
-    // phases: phase A writes a new path into it, phase B reads the ray, the shading thread of phase C updates it in
-    // place. Nothing of it stays in registers across the traversal, which is what used to spill (and the spill lines
-    // competed with the BVH for L1). When a path ends the SHADING thread also starts the pixel's next sample in the
-    // column (word 19 = sample index): terminated segments sit together after the sort, so whole warps generate camera
-    // rays instead of scattered lanes of every warp.
-    float *col = s_state + tid;
-    // CPURenderer.cpp:431-452 + the camera ray: sample `sample` of pixel (pi, pj) written into column c. Inlined at
-    // both call sites on purpose: as an out-of-line function it measured 2.6 % slower (19.89 vs 19.38 ms per 32 spp).
+    // Every column of the shared-memory array is one pixel's path slot: ray 0-5, throughput 6-8, rng 9-12, hit 13-17,
+    // (sample index << 8 | bounce) 18, the pixel's accumulator 19-22. Threads are WORKERS, not owners: after the sort,
+    // thread k shades the k-th segment, adds a finished sample to the column's accumulator, starts the pixel's next
+    // sample there, and goes straight on to trace the ray it has just produced - no barrier between shading and
+    // tracing, so a CTA waits once per segment (before the sort), not twice. One column is touched by one thread per
+    // iteration and a pixel's samples end in order, so the sums are those of the owner-thread forms, bit for bit.
     auto start_path = [&](float *c, uint32_t pi, uint32_t pj, uint32_t sample) {
         const uint32_t frame_seed = a.first_sample + sample * a.sample_stride; // CPURenderer.cpp:442-443
         Rng rng = rng_seed(pj * a.width + pi + frame_seed * a.width * a.height);
@@ -461,49 +456,50 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
         c[10 * T] = __uint_as_float(rng.s1);
         c[11 * T] = __uint_as_float(rng.s2);
         c[12 * T] = __uint_as_float(rng.s3);
-        c[18 * T] = __uint_as_float(0u); // bounce
-        c[19 * T] = __uint_as_float(sample);
+        c[18 * T] = __uint_as_float(sample << 8); // sample index : 24 | bounce : 8
     };
-    live = in_image && a.sample_count > 0u;
-    if (live)
+    float *mine = s_state + tid; // the column this thread works on in the current iteration
+    bool have = in_image && a.sample_count > 0u;
+    if (in_image)
     {
-        start_path(col, i, j, 0u);
+        const float4 acc = accum[size_t(j) * a.width + i];
+        mine[19 * T] = acc.x;
+        mine[20 * T] = acc.y;
+        mine[21 * T] = acc.z;
+        mine[22 * T] = acc.w;
     }
+    if (have)
+    {
+        start_path(mine, i, j, 0u);
+    }
+    if (tid < 64)
+    {
+        s_bin[tid >> 5][tid & 31u] = 0;
+    }
+    __syncthreads();
+    uint32_t parity = 0;
     for (;;)
     {
-        if (tid < 32)
+        // ---- trace the segment in this thread's column, park the hit, count its shading class
+        uint32_t key = 0, pos = 0;
+        if (have)
         {
-            s_bin[tid] = 0;
-        }
-        if (!__syncthreads_or(live))
-        {
-            break;
-        }
-        // ---- phase B: one path segment
-        Hit hit;
-        hit.t = 0.f;
-        hit.u = 0.f;
-        hit.v = 0.f;
-        hit.inst = SPK_INVALID_ID;
-        hit.face = SPK_INVALID_ID;
-        if (live)
-        {
-            const V3 origin = mk(col[0 * T], col[1 * T], col[2 * T]), dir = mk(col[3 * T], col[4 * T], col[5 * T]);
+            Hit hit;
+            const V3 origin = mk(mine[0 * T], mine[1 * T], mine[2 * T]), dir = mk(mine[3 * T], mine[4 * T], mine[5 * T]);
             trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
             rays++;
+            mine[13 * T] = hit.t;
+            mine[14 * T] = hit.u;
+            mine[15 * T] = hit.v;
+            mine[16 * T] = __uint_as_float(hit.inst);
+            mine[17 * T] = __uint_as_float(hit.face);
+            key = shade_class(sc, hit.inst);
+            pos = atomicAdd(&s_bin[parity][key], 1u);
         }
-        // ---- phase C: park the hit, sort by class, shade the sorted segment, hand the outcome back
-        col[13 * T] = hit.t;
-        col[14 * T] = hit.u;
-        col[15 * T] = hit.v;
-        col[16 * T] = __uint_as_float(hit.inst);
-        col[17 * T] = __uint_as_float(hit.face);
-        const uint32_t key = live ? shade_class(sc, hit.inst) : 31u;
-        const uint32_t pos = atomicAdd(&s_bin[key], 1u);
         __syncthreads();
         if (tid < 32)
         {
-            uint32_t c = s_bin[tid], incl = c;
+            uint32_t c = s_bin[parity][tid], incl = c;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1)
             {
@@ -513,15 +509,31 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                     incl += t;
                 }
             }
-            s_bin[tid] = incl - c; // exclusive start of the class
+            s_bin[parity][tid] = incl - c; // exclusive start of the class
+            s_bin[parity ^ 1u][tid] = 0;   // the other set was last read before the previous iteration's last barrier
+            if (tid == 31)
+            {
+                s_total = incl;
+            }
         }
         __syncthreads();
-        const uint32_t n_live = s_bin[31]; // dead lanes are the last class
-        s_sorted[s_bin[key] + pos] = tid;
-        __syncthreads();
-        if (tid < n_live)
+        const uint32_t n_live = s_total;
+        if (n_live == 0u)
         {
-            float *src = s_state + s_sorted[tid];
+            break;
+        }
+        if (have)
+        {
+            s_sorted[s_bin[parity][key] + pos] = (uint16_t)(mine - s_state);
+        }
+        __syncthreads();
+        parity ^= 1u;
+        have = tid < n_live;
+        if (have)
+        {
+            const uint32_t column = s_sorted[tid];
+            float *src = s_state + column;
+            mine = src;
             V3 o = mk(src[0 * T], src[1 * T], src[2 * T]), d = mk(src[3 * T], src[4 * T], src[5 * T]);
             V3 thr = mk(src[6 * T], src[7 * T], src[8 * T]);
             Hit h;
@@ -530,7 +542,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             h.v = src[15 * T];
             h.inst = __float_as_uint(src[16 * T]);
             h.face = __float_as_uint(src[17 * T]);
-            uint32_t b = __float_as_uint(src[18 * T]);
+            const uint32_t packed = __float_as_uint(src[18 * T]);
+            const uint32_t sample = packed >> 8;
+            uint32_t b = packed & 255u;
             V3 color = mk(0.f, 0.f, 0.f);
             float valid = 1.f;
             bool done = false;
@@ -600,40 +614,18 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                             src[10 * T] = __uint_as_float(r.s1);
                             src[11 * T] = __uint_as_float(r.s2);
                             src[12 * T] = __uint_as_float(r.s3);
-                            src[18 * T] = __uint_as_float(b);
+                            src[18 * T] = __uint_as_float((sample << 8) | b);
                         }
                     }
                 }
             }
-            // outcome in the hit words: colour, valid flag, done flag
-            src[13 * T] = color.x;
-            src[14 * T] = color.y;
-            src[15 * T] = color.z;
-            src[16 * T] = valid;
-            src[17 * T] = __uint_as_float(done ? 1u : 0u);
             if (done)
             {
-                const uint32_t next_sample = __float_as_uint(src[19 * T]) + 1u;
-                if (next_sample < a.sample_count)
-                {
-                    const uint32_t owner = s_sorted[tid], owarp = blockIdx.x * WARPS + (owner >> 5), olane = owner & 31u;
-                    start_path(src, (owarp % tiles_x) * kTileW + (olane & (kTileW - 1)),
-                               (owarp / tiles_x) * kTileH + (olane / kTileW), next_sample);
-                }
-            }
-        }
-        __syncthreads();
-        if (live)
-        {
-            const bool done = __float_as_uint(col[17 * T]) != 0u;
-            if (done)
-            {
-                V3 color = mk(col[13 * T], col[14 * T], col[15 * T]);
-                const float valid = col[16 * T];
                 color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
+                float4 acc = make_float4(src[19 * T], src[20 * T], src[21 * T], src[22 * T]);
                 if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
                 {
-                    uint32_t n = a.cumulated + s;
+                    uint32_t n = a.cumulated + sample;
                     float ma = (float)n / (float)(n + 1u);
                     acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
                                       lerp1(valid, acc.w, ma));
@@ -642,16 +634,27 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                 {
                     acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
                 }
-                s++;
-                live = s < a.sample_count; // the shading thread has already put the next sample into the column
+                src[19 * T] = acc.x;
+                src[20 * T] = acc.y;
+                src[21 * T] = acc.z;
+                src[22 * T] = acc.w;
+                if (sample + 1u < a.sample_count)
+                {
+                    uint32_t pi, pj;
+                    pixel_of(column, pi, pj);
+                    start_path(src, pi, pj, sample + 1u);
+                }
+                else
+                {
+                    have = false; // the pixel has all its samples: the column stays out of the next sort
+                }
             }
-            // else: the shading thread left the next segment in this column
         }
-        // (the barrier at the top of the loop separates these reads from the next iteration's column writes)
     }
     if (in_image)
     {
-        accum[size_t(j) * a.width + i] = acc;
+        const float *own = s_state + tid;
+        accum[size_t(j) * a.width + i] = make_float4(own[19 * T], own[20 * T], own[21 * T], own[22 * T]);
     }
     uint32_t total = __reduce_add_sync(0xffffffffu, rays);
     uint32_t pixels = __popc(__ballot_sync(0xffffffffu, in_image));
@@ -685,7 +688,7 @@ template <int W, int B> cudaError_t sorted_allow_smem()
     if (e == cudaSuccess)                                                                                              \
         e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);    \
     if (e == cudaSuccess)                                                                                              \
-        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B>, bytes + (W * 32 + 32) * 4, B);
+        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B>, bytes + W * 32 * 2 + 2 * 32 * 4 + 16, B);
         SPK_ALLOW(true, false)
         SPK_ALLOW(false, false)
         SPK_ALLOW(true, true)
@@ -768,7 +771,9 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
         return e ? atoi(e) : -1;
     }();
     int phased = phased_setting >= 0 ? phased_setting : ctx->mega_variant;
-    if (phased >= 1000 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE) && a.max_bounce != 0u && a.debug == 0u)
+    // (the sorted kernel packs sample index : 24 | bounce : 8 into one word of its path slot)
+    if (phased >= 1000 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE) && a.max_bounce != 0u && a.debug == 0u &&
+        a.max_bounce <= 255u && a.sample_count < (1u << 24))
     {
         // SPK_RENDER_PHASED = 1000 + warps*10 + min_blocks: render_sorted_kernel
 #define SPK_SORTED_CASE(W, B)                                                                                          \
