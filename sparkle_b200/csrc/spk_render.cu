@@ -983,11 +983,13 @@ int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavef
     SPK_CUDA_TRY(cudaEventCreate(&e1));
     float ms[2] = {3.4e38f, 0.f};
     int rc = SPK_OK;
-    // candidates: the megakernel forms (phased; sorted with 16 warps x 2 CTAs/SM and 8 warps x 4 CTAs/SM), then wavefront
-    // a later form replaces the incumbent only when it is more than 3 % faster (4-spp timings of near-equal forms are noise)
-    static const int kForms[4] = {1162, 831, 1084, -1};
+    // candidates: the sorted megakernel with 16 warps x 2 CTAs/SM and with 8 warps x 4 CTAs/SM, then the wavefront tracer
+    // (the phased kernel has not won on any scene since the sorted form keeps its path slots in shared memory; it stays
+    // as the fallback for probes, zero-bounce and > 255-bounce launches). A later form replaces the incumbent only when
+    // it is more than 3 % faster: short timings of near-equal forms are noise.
+    static const int kForms[3] = {1162, 1084, -1};
     int best_form = kForms[0];
-    for (int which = 0; which < 4 && rc == SPK_OK; which++)
+    for (int which = 0; which < 3 && rc == SPK_OK; which++)
     {
         float best = 3.4e38f;
         for (int rep = 0; rep < 2 && rc == SPK_OK; rep++) // first repetition warms caches and lazy module loading
