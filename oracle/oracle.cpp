@@ -39,6 +39,19 @@ namespace
 constexpr float kEps = 1e-6f;
 constexpr float kTolerance = 1e-4f;
 constexpr float kPi = 3.14159274101257324f;        // std::numbers::pi_v<float>
+
+// libm mode (orc_set_libm, port only). 0 = glibc's float routines, what the reference calls (default; every parity pin
+// against the reference uses it). 1 = "device libm": sin, cos and pow evaluated in double and rounded once to float, which
+// is what the CUDA path does (spk_shade.cuh ref_sincos / ref_pow / ref_pow5). The two differ by one ulp for ~1 % of
+// arguments; mode 1 lets a test separate "the GPU follows the reference's operation order" (GPU == port in mode 1, to
+// accumulation rounding) from "how far one-ulp libm differences move an image" (port mode 1 vs reference, CPU only).
+int g_libm_mode = 0;
+inline float m_sin(float x) { return g_libm_mode ? static_cast<float>(std::sin(static_cast<double>(x))) : std::sin(x); }
+inline float m_cos(float x) { return g_libm_mode ? static_cast<float>(std::cos(static_cast<double>(x))) : std::cos(x); }
+inline float m_pow(float x, float y)
+{
+    return g_libm_mode ? static_cast<float>(std::pow(static_cast<double>(x), static_cast<double>(y))) : std::pow(x, y);
+}
 constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<float>
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -135,8 +148,8 @@ inline void unit_disk(Rng &r, float &x, float &y)
     float rand = rng_unit(r);
     float theta = rng_unit(r) * 2.0f * kPi;
     float rad = std::sqrt(rand);
-    x = rad * std::cos(theta);
-    y = rad * std::sin(theta);
+    x = rad * m_cos(theta);
+    y = rad * m_sin(theta);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -239,7 +252,7 @@ inline F4 access_pixel(const SpkTextureDesc &t, uint32_t x, uint32_t y)
 inline float srgb_to_linear(float c)
 {
     float cutoff = c < 0.04045f ? 1.f : 0.f;
-    float higher = std::pow((c + 0.055f) / 1.055f, 2.4f);
+    float higher = m_pow((c + 0.055f) / 1.055f, 2.4f);
     float lower = c / 12.92f;
     return higher * (1.f - cutoff) + lower * cutoff;
 }
@@ -733,7 +746,7 @@ inline MaterialSample material_sample(const SpkSceneDesc *d, const SpkMaterialDe
 
 // ---------------------------------------------------------------------------------------------------------------------
 // a12/a13. BxDF helpers: Utilities.h:291-299 (SchlickApproximation), :301-324 (FrDielectric), :434-451 (Smith/Schlick GGX)
-inline float schlick(float cos_i, float r0) { return r0 + (1.f - r0) * std::pow(1.f - cos_i, 5.f); }
+inline float schlick(float cos_i, float r0) { return r0 + (1.f - r0) * m_pow(1.f - cos_i, 5.f); }
 
 inline float smith_ggx_correlated(float cos_o, float cos_i, float roughness)
 {
@@ -760,7 +773,7 @@ inline V3 sample_vndf(Rng &rng, V3 wo, float roughness)
     V3 t2 = cross(v, t1);
     float r = std::sqrt(u1);
     float phi = 2.f * kPi * u2;
-    float p1 = r * std::cos(phi), p2 = r * std::sin(phi);
+    float p1 = r * m_cos(phi), p2 = r * m_sin(phi);
     float s = 0.5f * (1.f + v.z);
     p2 = (1.f - s) * std::sqrt(1.f - p1 * p1) + s * p2;
     float c = std::sqrt(std::max(0.f, 1.f - p1 * p1 - p2 * p2));
@@ -836,7 +849,7 @@ V3 sample_surface(const SceneView &sv, Rng &rng, const Surface &sf, V3 ray_dir, 
         {
             if (rng_unit(rng) < ms.metallic)
             {
-                float f = std::pow(1.f - local_cos_i, 5.f); // SchlickApproximation(cos, Vector3 r0)
+                float f = m_pow(1.f - local_cos_i, 5.f); // SchlickApproximation(cos, Vector3 r0)
                 fresnel_color = mk(ms.base_color.x + (1.f - ms.base_color.x) * f,
                                    ms.base_color.y + (1.f - ms.base_color.y) * f,
                                    ms.base_color.z + (1.f - ms.base_color.z) * f);
@@ -1094,6 +1107,12 @@ inline SpkHit to_hit(const Candidate &c)
 extern "C"
 {
 const char *orc_kind(void) { return "port"; }
+
+int orc_set_libm(uint32_t mode)
+{
+    g_libm_mode = mode ? 1 : 0;
+    return 0;
+}
 
 void orc_rng_state(uint32_t seed, uint32_t state_out[4])
 {
@@ -1465,9 +1484,9 @@ int orc_resolve(const float *accum, uint32_t width, uint32_t height, uint32_t ac
             else
             {
                 uint8_t *q = static_cast<uint8_t *>(out) + o * 4;
-                q[0] = static_cast<uint8_t>(std::pow(r, 0.45f) * 255.f);
-                q[1] = static_cast<uint8_t>(std::pow(g, 0.45f) * 255.f);
-                q[2] = static_cast<uint8_t>(std::pow(b, 0.45f) * 255.f);
+                q[0] = static_cast<uint8_t>(m_pow(r, 0.45f) * 255.f);
+                q[1] = static_cast<uint8_t>(m_pow(g, 0.45f) * 255.f);
+                q[2] = static_cast<uint8_t>(m_pow(b, 0.45f) * 255.f);
                 q[3] = 255;
             }
         }

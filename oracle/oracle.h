@@ -61,6 +61,20 @@ uint32_t orc_kat_sample_surface(const SpkSceneDesc *scene, uint32_t material, ui
                                 const float *normal, const float *tangent, const float *uv, float *out_wi,
                                 float *out_throughput);
 
+/* a17 + transforms ("reference" only: these pin the PRODUCT's host math, the port has no copy).
+ * orc_kat_transform: SceneNode::SetTransform(translate, euler radians, scale) under the identity root -> rows 0..2 of
+ * Transform::GetMatrix() and of GetInverse().GetMatrix() (Transform.cpp:52-64). orc_kat_camera: OrbitCameraComponent::Setup
+ * parameters (degrees) + CameraComponent attribute -> CameraRenderProxy posture / focus plane (CameraRenderProxy.cpp:21-33,
+ * 113-136) as an SpkCamera. */
+int orc_kat_transform(const float *translate, const float *euler, const float *scale, float *fwd12, float *inv12);
+int orc_kat_camera(const float *center, float radius, float pitch_deg, float yaw_deg, float focal_length,
+                   float sensor_height, float aperture, float exposure, uint32_t width, uint32_t height, SpkCamera *out);
+/* GLTFLoader::ProcessNode transform of a root-level node (GLTFLoader.cpp:532-544): translation, rotation xyzw */
+int orc_kat_gltf_node(const float *translation, const float *rotation_xyzw, float *fwd12, float *inv12);
+/* "port" only: 0 = glibc float sin/cos/pow as the reference calls them (default), 1 = evaluated in double and rounded
+ * once, as the CUDA path does (separates operation-order parity from one-ulp libm drift; oracle.cpp g_libm_mode) */
+int orc_set_libm(uint32_t mode);
+
 /* a6-a9: closest hit of a ray batch. threads<=1 runs on the calling thread. */
 int orc_trace_closest(const SpkSceneDesc *scene, const SpkRay *rays, uint64_t num_rays, SpkHit *hits, uint32_t mode,
                       uint32_t threads, OrcCounters *counters);

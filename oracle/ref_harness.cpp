@@ -585,6 +585,98 @@ void orc_kat_sky(const SpkSkyDesc *sky, const float *direction, float *out)
     out[2] = c.z();
 }
 
+// a17 / transforms. The scene-graph classes (SceneNode, OrbitCameraComponent, CameraComponent) pull the whole app in, so
+// the few lines of theirs on this path are restated here WITH THE SAME Eigen expressions (so the compiler emits the same
+// float operations), and everything below them is the reference's own compiled code: Transform::Update /
+// UpdateTransformData / GetInverse (Transform.cpp:7-15,52-64, Transform.h:110-126) and
+// CameraRenderProxy::OnTransformDirty (CameraRenderProxy.cpp:113-136).
+int orc_kat_transform(const float *translate, const float *euler, const float *scale, float *fwd, float *inv)
+{
+    // SceneNode::SetTransform(translate, Vector3 rotation, scale) -> Transform::Update(.., EulerRotationToRotationAxis(..), ..)
+    // (SceneNode.h:71-76, Transform.h:40-43); a node under the identity root: world == local (SceneNode.cpp:30-44)
+    Transform t;
+    t.Update(Vector3(translate[0], translate[1], translate[2]), Vector3(euler[0], euler[1], euler[2]),
+             Vector3(scale[0], scale[1], scale[2]));
+    const auto &m = t.GetMatrix();
+    const Transform it = t.GetInverse(); // what MeshRenderProxy uses for the object-space ray (MeshRenderProxy.cpp:99-100)
+    const auto &im = it.GetMatrix();
+    for (int r = 0; r < 3; r++)
+    {
+        for (int c = 0; c < 4; c++)
+        {
+            fwd[r * 4 + c] = m(r, c);
+            inv[r * 4 + c] = im(r, c);
+        }
+    }
+    return 0;
+}
+
+// GLTFLoader ProcessNode's transform lines (io/scene/GLTFLoader.cpp:532-544; tinygltf is absent, so the loader itself
+// cannot be compiled): rotation = AngleAxis(90 deg, Right) * node.rotation, SetTransform(translation, normalized, Ones),
+// for a node directly under the identity scene root. q = glTF xyzw.
+int orc_kat_gltf_node(const float *translation, const float *q, float *fwd, float *inv)
+{
+    Rotation rotation = utilities::Vector4AsQuaternion(Vector4(q[0], q[1], q[2], q[3]));
+    rotation = Eigen::AngleAxis<Scalar>(utilities::ToRadian(90.0f), Right) * rotation;
+    Transform t;
+    t.Update(Vector3(translation[0], translation[1], translation[2]), rotation.normalized(), Vector3(Ones));
+    const auto &m = t.GetMatrix();
+    const Transform it = t.GetInverse();
+    const auto &im = it.GetMatrix();
+    for (int r = 0; r < 3; r++)
+    {
+        for (int c = 0; c < 4; c++)
+        {
+            fwd[r * 4 + c] = m(r, c);
+            inv[r * 4 + c] = im(r, c);
+        }
+    }
+    return 0;
+}
+
+int orc_kat_camera(const float *center, float radius, float pitch, float yaw, float focal_length, float sensor_height,
+                   float aperture, float exposure, uint32_t width, uint32_t height, SpkCamera *out)
+{
+    // OrbitCameraComponent::UpdateTransform (OrbitCameraComponent.cpp:16-30)
+    const Vector3 relative_rotation = utilities::ToRadian(Vector3(-pitch, 0.f, -yaw));
+    auto rotation_transform =
+        Eigen::AngleAxis<Scalar>(relative_rotation.z(), Up) * Eigen::AngleAxis<Scalar>(relative_rotation.x(), Right);
+    const Vector3 relative_direction = rotation_transform * Front;
+    const Vector3 position = relative_direction * -radius + Vector3(center[0], center[1], center[2]);
+    Transform node; // GetNode()->SetTransform(position, -relative_rotation)
+    node.Update(position, Vector3(-relative_rotation), Vector3(Ones));
+    // CalculateRenderAttribute (CameraComponent.cpp:120-128), SetFocusDistance(radius_)
+    CameraRenderProxy cam;
+    cam.state_.vertical_fov = 2.f * std::atan(sensor_height / (2.f * focal_length));
+    cam.state_.focus_distance = radius;
+    cam.state_.exposure = exposure;
+    cam.state_.aperture_radius = focal_length / aperture * 0.5f;
+    cam.UpdateTransform(node);
+    // the attribute_dirty_ block of CameraRenderProxy::Update (CameraRenderProxy.cpp:21-33; Update itself uploads a UBO
+    // through the RHI and cannot run headless); AspectRatio: RenderResolution.h:25-28
+    cam.aspect_ratio_ = static_cast<float>(width) / static_cast<float>(height);
+    auto h = std::tan(cam.state_.vertical_fov / 2.f);
+    cam.focus_plane_.height = 2.f * h * cam.state_.focus_distance;
+    cam.focus_plane_.width = cam.aspect_ratio_ * cam.focus_plane_.height;
+    cam.SetupProjectionMatrix();
+    cam.OnTransformDirty(nullptr); // the reference's own code
+    auto put = [](float *dst, const Vector3 &v) {
+        dst[0] = v.x();
+        dst[1] = v.y();
+        dst[2] = v.z();
+    };
+    put(out->position, cam.posture_.position);
+    put(out->up, cam.posture_.up);
+    put(out->front, cam.posture_.front);
+    put(out->right, cam.posture_.right);
+    put(out->max_u, cam.focus_plane_.max_u);
+    put(out->max_v, cam.focus_plane_.max_v);
+    put(out->lower_left, cam.focus_plane_.lower_left);
+    out->aperture_radius = cam.state_.aperture_radius;
+    out->exposure = cam.state_.exposure;
+    return 0;
+}
+
 uint32_t orc_kat_sample_surface(const SpkSceneDesc *scene, uint32_t material, uint32_t seed, const float *dir,
                                 const float *normal, const float *tangent, const float *uv, float *out_wi,
                                 float *out_throughput)

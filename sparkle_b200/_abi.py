@@ -144,6 +144,10 @@ HOST_SYMBOLS = {
     "spk_host_scene_desc": (C.POINTER(SceneDesc), [C.c_void_p]),
     "spk_host_scene_free": (None, [C.c_void_p]),
     "spk_host_gltf_probe": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_uint64)]),
+    # host/ref_math.h: Transform / orbit camera in the reference's float operation order
+    "spk_host_trs": (None, [fp, fp, fp, fp, fp]),
+    "spk_host_gltf_node": (None, [fp, fp, fp, fp]),
+    "spk_host_orbit_camera": (None, [fp, f32, f32, f32, f32, f32, f32, f32, u32, u32, C.POINTER(Camera)]),
 }
 
 _libs = {}

@@ -55,21 +55,16 @@ class Xoshiro128Plus:
 
 
 def trs(translate=(0, 0, 0), euler=(0, 0, 0), scale=(1, 1, 1)):
-    """Transform(translate, euler, scale): Translation * (Rx * Ry * Rz) * Scaling (Transform.cpp:62-63,
-    Utilities.h:392-396). Returns (fwd, inv) as float32 3x4 row-major arrays."""
-    rx, ry, rz = [float(a) for a in euler]
-    cx, sx, cy, sy, cz, sz = math.cos(rx), math.sin(rx), math.cos(ry), math.sin(ry), math.cos(rz), math.sin(rz)
-    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
-    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
-    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
-    R = Rx @ Ry @ Rz
-    S = np.diag(np.asarray(scale, np.float64))
-    M = np.eye(4)
-    M[:3, :3] = R @ S
-    M[:3, 3] = np.asarray(translate, np.float64)
-    M32_ = M.astype(f32).astype(np.float64)  # the inverse is taken of the float matrix, as Eigen does
-    Minv = np.linalg.inv(M32_)
-    return np.ascontiguousarray(M[:3, :].astype(f32)), np.ascontiguousarray(Minv[:3, :].astype(f32))
+    """Transform(translate, euler, scale): Translation * (Rx * Ry * Rz as quaternions) * Scaling and its affine inverse
+    (Transform.cpp:52-64, Utilities.h:392-396), computed by the host library in the reference's float operation order
+    (sparkle_b200/host/ref_math.cpp; bit-identical to the reference's Eigen code, tests/test_host_cpu.py).
+    Returns (fwd, inv) as float32 3x4 row-major arrays."""
+    from . import _abi as A
+    t, e, s = (np.ascontiguousarray(v, f32) for v in (translate, euler, scale))
+    fwd, inv = np.empty(12, f32), np.empty(12, f32)
+    A.host_lib().spk_host_trs(t.ctypes.data_as(A.fp), e.ctypes.data_as(A.fp), s.ctypes.data_as(A.fp),
+                              fwd.ctypes.data_as(A.fp), inv.ctypes.data_as(A.fp))
+    return fwd.reshape(3, 4), inv.reshape(3, 4)
 
 
 class MeshData:

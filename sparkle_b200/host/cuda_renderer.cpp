@@ -4,6 +4,7 @@
  * renderer fails to initialise, logs, and CreateRenderer returns nullptr (AppFramework.cpp:200-205 convention).
  */
 #include "cuda_renderer.h"
+#include "ref_math.h"
 
 #include <algorithm>
 #include <cctype>
@@ -35,36 +36,6 @@ std::string Lower(std::string s)
 
 constexpr float kPi = 3.14159274101257324f;
 
-// 3x3 float helpers (row-major)
-struct Mat3
-{
-    float m[9];
-};
-Mat3 Mul(const Mat3 &a, const Mat3 &b)
-{
-    Mat3 r{};
-    for (int i = 0; i < 3; i++)
-    {
-        for (int j = 0; j < 3; j++)
-        {
-            float s = 0.f;
-            for (int k = 0; k < 3; k++)
-            {
-                s += a.m[3 * i + k] * b.m[3 * k + j];
-            }
-            r.m[3 * i + j] = s;
-        }
-    }
-    return r;
-}
-Mat3 RotX(float a) { return Mat3{{1, 0, 0, 0, std::cos(a), -std::sin(a), 0, std::sin(a), std::cos(a)}}; }
-Mat3 RotY(float a) { return Mat3{{std::cos(a), 0, std::sin(a), 0, 1, 0, -std::sin(a), 0, std::cos(a)}}; }
-Mat3 RotZ(float a) { return Mat3{{std::cos(a), -std::sin(a), 0, std::sin(a), std::cos(a), 0, 0, 0, 1}}; }
-Vec3 Apply(const Mat3 &r, Vec3 v)
-{
-    return Vec3{r.m[0] * v.x + r.m[1] * v.y + r.m[2] * v.z, r.m[3] * v.x + r.m[4] * v.y + r.m[5] * v.z,
-                r.m[6] * v.x + r.m[7] * v.y + r.m[8] * v.z};
-}
 } // namespace
 
 const std::string &LastError() { return g_last_error; }
@@ -205,28 +176,10 @@ void RenderConfig::Validate()
 // ---- Transform -----------------------------------------------------------------------------------------------------------
 void Transform::Matrices(float fwd[12], float inv[12]) const
 {
-    // Translation * (Rx * Ry * Rz) * Scaling (Transform.cpp:62-63, utilities::EulerRotationToRotationAxis
-    // Utilities.h:392-396); the inverse of an affine TRS in closed form: S^-1 * R^T * (p - t)
-    Mat3 r = Mul(Mul(RotX(euler.x), RotY(euler.y)), RotZ(euler.z));
-    const float s[3] = {scale.x, scale.y, scale.z}, t[3] = {translation.x, translation.y, translation.z};
-    for (int i = 0; i < 3; i++)
-    {
-        for (int j = 0; j < 3; j++)
-        {
-            fwd[4 * i + j] = r.m[3 * i + j] * s[j];
-        }
-        fwd[4 * i + 3] = t[i];
-    }
-    for (int i = 0; i < 3; i++)
-    {
-        float acc = 0.f;
-        for (int j = 0; j < 3; j++)
-        {
-            inv[4 * i + j] = r.m[3 * j + i] / s[i];
-            acc += inv[4 * i + j] * t[j];
-        }
-        inv[4 * i + 3] = -acc;
-    }
+    // Transform::UpdateTransformData (Transform.cpp:52-64) in the reference's float operation order: ref_math.cpp
+    const float t[3] = {translation.x, translation.y, translation.z}, e[3] = {euler.x, euler.y, euler.z},
+                s[3] = {scale.x, scale.y, scale.z};
+    refmath::TrsMatrices(t, e, s, fwd, inv);
 }
 
 // ---- meshes --------------------------------------------------------------------------------------------------------------
@@ -313,20 +266,16 @@ MeshData MeshData::UnitSphere(uint32_t v_size)
 void CameraProxy::SetupOrbit(Vec3 center, float radius, float pitch_deg, float yaw_deg, float focal_length,
                              float sensor_height, float aperture, float exposure)
 {
-    // OrbitCameraComponent::UpdateTransform: rotation = AngleAxis(-yaw, Up) * AngleAxis(-pitch, Right); the node's
-    // rotation is the inverse, whose rows are right / front / up (Transform::ExtractLocalBasis, Transform.h:121-126)
-    const float rx = -pitch_deg * kPi / 180.f, rz = -yaw_deg * kPi / 180.f;
-    Mat3 rot = Mul(RotZ(rz), RotX(rx));
-    Vec3 dir = Apply(rot, Vec3{0.f, 1.f, 0.f});
-    position_ = Vec3{dir.x * -radius + center.x, dir.y * -radius + center.y, dir.z * -radius + center.z};
-    right_ = Vec3{rot.m[0], rot.m[3], rot.m[6]}; // rows of rot^T
-    front_ = Vec3{rot.m[1], rot.m[4], rot.m[7]};
-    up_ = Vec3{rot.m[2], rot.m[5], rot.m[8]};
-    // CalculateRenderAttribute (CameraComponent.cpp:120-128)
-    state_.vertical_fov = 2.f * std::atan(sensor_height / (2.f * focal_length));
-    state_.focus_distance = radius; // SetFocusDistance(radius_)
-    state_.exposure = exposure;
-    state_.aperture_radius = focal_length / aperture * 0.5f;
+    // kept as given: Update() turns them into posture and focus plane once the resolution is known (ref_math.cpp follows
+    // OrbitCameraComponent::UpdateTransform, CalculateRenderAttribute and CameraRenderProxy::Update / OnTransformDirty)
+    orbit_center_ = center;
+    orbit_radius_ = radius;
+    orbit_pitch_ = pitch_deg;
+    orbit_yaw_ = yaw_deg;
+    focal_length_ = focal_length;
+    sensor_height_ = sensor_height;
+    aperture_ = aperture;
+    exposure_ = exposure;
     attribute_dirty_ = true;
     transform_dirty_ = true;
 }
@@ -340,34 +289,11 @@ void CameraProxy::MarkPixelDirty()
 
 void CameraProxy::Update(const RenderConfig &config)
 {
-    float width = 0.f, height = 0.f;
     if (attribute_dirty_ || transform_dirty_)
     {
-        const float aspect = static_cast<float>(config.image_width) / static_cast<float>(config.image_height);
-        const float h = std::tan(state_.vertical_fov / 2.f);
-        height = 2.f * h * state_.focus_distance;
-        width = aspect * height;
-        // OnTransformDirty (CameraRenderProxy.cpp:113-136)
-        auto put = [](float *dst, Vec3 v) {
-            dst[0] = v.x;
-            dst[1] = v.y;
-            dst[2] = v.z;
-        };
-        Vec3 max_u{right_.x * width, right_.y * width, right_.z * width};
-        Vec3 max_v{up_.x * height, up_.y * height, up_.z * height};
-        const float f = state_.focus_distance;
-        Vec3 ll{position_.x + front_.x * f - max_u.x * .5f - max_v.x * .5f,
-                position_.y + front_.y * f - max_u.y * .5f - max_v.y * .5f,
-                position_.z + front_.z * f - max_u.z * .5f - max_v.z * .5f};
-        put(camera_.position, position_);
-        put(camera_.up, up_);
-        put(camera_.front, front_);
-        put(camera_.right, right_);
-        put(camera_.max_u, max_u);
-        put(camera_.max_v, max_v);
-        put(camera_.lower_left, ll);
-        camera_.aperture_radius = state_.aperture_radius;
-        camera_.exposure = state_.exposure;
+        const float c[3] = {orbit_center_.x, orbit_center_.y, orbit_center_.z};
+        refmath::OrbitCamera(c, orbit_radius_, orbit_pitch_, orbit_yaw_, focal_length_, sensor_height_, aperture_,
+                             exposure_, config.image_width, config.image_height, &camera_);
         attribute_dirty_ = false;
         transform_dirty_ = false;
         pixels_dirty_ = true;

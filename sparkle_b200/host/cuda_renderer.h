@@ -129,8 +129,9 @@ public:
     [[nodiscard]] const SpkCamera &Get() const { return camera_; }
 
 private:
-    Vec3 position_, right_{1, 0, 0}, front_{0, 1, 0}, up_{0, 0, 1};
-    CameraAttribute state_;
+    Vec3 orbit_center_;
+    float orbit_radius_ = 25.f, orbit_pitch_ = 10.f, orbit_yaw_ = -20.f;
+    float focal_length_ = 0.035f, sensor_height_ = 0.024f, aperture_ = 22.f, exposure_ = 1.f;
     SpkCamera camera_{};
     bool attribute_dirty_ = true, transform_dirty_ = true, pixels_dirty_ = true;
     uint32_t cumulated_sample_count_ = 0, pending_sample_count_ = 0;

@@ -1,5 +1,6 @@
 /* gltf_loader.cpp — see gltf_loader.h. Host code only; nothing here touches the device. */
 #include "gltf_loader.h"
+#include "ref_math.h"
 
 #include <zlib.h>
 
@@ -570,64 +571,41 @@ bool ReadIndices(Model &m, int accessor_id, std::vector<uint32_t> &out)
     return true;
 }
 
-// ---- rigid transforms (float, like the reference's Eigen types) ------------------------------------------------------
-struct Quat
+// ---- node transforms ------------------------------------------------------------------------------------------------
+// A node's local transform is Transform(translation, rotation, Ones) with the y-up -> z-up rotation in front
+// (GLTFLoader.cpp:532-544), computed in the reference's float operation order by ref_math.cpp (bit-identical for nodes
+// directly under the scene root: tests/test_host_cpu.py). Children compose like SceneNode::UpdateDirtyTransform
+// (SceneNode.cpp:30-44): world = parent * local, world^-1 = local^-1 * parent^-1, as 3x4 affine products.
+struct Affine
 {
-    float x = 0, y = 0, z = 0, w = 1;
+    float fwd[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    float inv[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    bool identity = true;
 };
-Quat Mul(const Quat &a, const Quat &b)
-{
-    return Quat{a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y, a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x,
-                a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w, a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z};
-}
-Quat Normalized(const Quat &q)
-{
-    float n = std::sqrt(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-    return n > 0.f ? Quat{q.x / n, q.y / n, q.z / n, q.w / n} : Quat{};
-}
-struct Rigid // rotation (row-major 3x3) + translation
-{
-    float r[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
-    float t[3] = {0, 0, 0};
-};
-Rigid FromTR(const float t[3], const Quat &q)
-{
-    Rigid m;
-    const float xx = q.x * q.x, yy = q.y * q.y, zz = q.z * q.z, xy = q.x * q.y, xz = q.x * q.z, yz = q.y * q.z,
-                wx = q.w * q.x, wy = q.w * q.y, wz = q.w * q.z;
-    const float r[9] = {1 - 2 * (yy + zz), 2 * (xy - wz), 2 * (xz + wy), 2 * (xy + wz), 1 - 2 * (xx + zz),
-                        2 * (yz - wx),     2 * (xz - wy), 2 * (yz + wx), 1 - 2 * (xx + yy)};
-    memcpy(m.r, r, sizeof(r));
-    memcpy(m.t, t, 12);
-    return m;
-}
-Rigid Compose(const Rigid &a, const Rigid &b) // a after b
-{
-    Rigid m;
-    for (int i = 0; i < 3; i++)
-    {
-        for (int j = 0; j < 3; j++)
-        {
-            m.r[3 * i + j] = a.r[3 * i] * b.r[j] + a.r[3 * i + 1] * b.r[3 + j] + a.r[3 * i + 2] * b.r[6 + j];
-        }
-        m.t[i] = a.r[3 * i] * b.t[0] + a.r[3 * i + 1] * b.t[1] + a.r[3 * i + 2] * b.t[2] + a.t[i];
-    }
-    return m;
-}
-void ToMatrices(const Rigid &m, float fwd[12], float inv[12])
+void Mul34(const float a[12], const float b[12], float out[12]) // a after b
 {
     for (int i = 0; i < 3; i++)
     {
-        float acc = 0.f;
-        for (int j = 0; j < 3; j++)
+        for (int j = 0; j < 4; j++)
         {
-            fwd[4 * i + j] = m.r[3 * i + j];
-            inv[4 * i + j] = m.r[3 * j + i]; // R^T
-            acc += m.r[3 * j + i] * m.t[j];
+            float v = (a[4 * i] * b[j] + a[4 * i + 1] * b[4 + j]) + a[4 * i + 2] * b[8 + j];
+            out[4 * i + j] = j == 3 ? v + a[4 * i + 3] : v;
         }
-        fwd[4 * i + 3] = m.t[i];
-        inv[4 * i + 3] = -acc;
     }
+}
+Affine Compose(const Affine &parent, const Affine &local)
+{
+    if (parent.identity)
+    {
+        Affine r = local; // identity * M is M bit for bit
+        r.identity = false;
+        return r;
+    }
+    Affine r;
+    Mul34(parent.fwd, local.fwd, r.fwd);
+    Mul34(local.inv, parent.inv, r.inv);
+    r.identity = false;
+    return r;
 }
 
 void ReadVec(const Json &node, const char *key, float *out, int n)
@@ -900,7 +878,7 @@ struct Loader
     }
 
     // ProcessNode (GLTFLoader.cpp:528-575)
-    bool Node(int node_id, const Rigid &parent, int depth)
+    bool Node(int node_id, const Affine &parent, int depth)
     {
         const auto &nodes = model.root.Arr("nodes");
         if (node_id < 0 || size_t(node_id) >= nodes.size() || depth > 256)
@@ -914,9 +892,10 @@ struct Loader
         ReadVec(node, "scale", s, 3);
         ReadVec(node, "rotation", q, 4);
         // glTF is y-up, the scene z-up: AngleAxis(90 deg, Right) * rotation, then normalized (:537-544)
-        const float h = 0.707106769084930419921875f; // float(sin 45 deg) = float(cos 45 deg)
-        const Quat rot = Normalized(Mul(Quat{h, 0.f, 0.f, h}, Quat{q[0], q[1], q[2], q[3]}));
-        const Rigid world = Compose(parent, FromTR(t, rot)); // scale stays Ones on the node
+        Affine local;
+        static const float ones[3] = {1.f, 1.f, 1.f};
+        refmath::TrsMatricesQuat(t, refmath::GltfNodeRotation(q), ones, local.fwd, local.inv); // scale stays Ones
+        const Affine world = Compose(parent, local);
         const int mesh_id = node.Int("mesh", -1);
         if (mesh_id >= 0)
         {
@@ -937,7 +916,6 @@ struct Loader
                     continue;
                 }
                 uint32_t mesh = 0, tris = 0;
-                static const float ones[3] = {1.f, 1.f, 1.f};
                 if (!Primitive(mesh_id, static_cast<int>(p), prims[p], instancing ? ones : s, mesh, tris))
                 {
                     return false;
@@ -957,7 +935,8 @@ struct Loader
                     material = default_material;
                 }
                 float fwd[12], inv[12];
-                ToMatrices(world, fwd, inv);
+                memcpy(fwd, world.fwd, sizeof(fwd));
+                memcpy(inv, world.inv, sizeof(inv));
                 if (instancing)
                 {
                     // world * Scaling(s): forward columns scaled, inverse rows divided
@@ -1035,7 +1014,7 @@ bool LoadGltf(const std::string &path, SceneProxy &scene, GltfStats *stats, cons
     }
     for (int r : roots)
     {
-        if (!loader.Node(r, Rigid{}, 0))
+        if (!loader.Node(r, Affine{}, 0))
         {
             return false;
         }

@@ -4,7 +4,6 @@ SceneRenderProxy::Update/UpdateBVH (libraries/source/renderer/proxy/SceneRenderP
 driver: primitives keep their registration order (== SpkHit.prim), the TLAS is built over world AABBs
 (AABB::TransformTo, core/math/AABB.h:57-78) and the BLAS over per-triangle boxes (MeshRenderProxy.cpp:31-65)."""
 import ctypes as C
-import math
 
 import numpy as np
 
@@ -204,28 +203,10 @@ class SceneBuilder:
 def orbit_camera(width, height, center=(0, 0, 0), radius=25.0, pitch=10.0, yaw=-20.0, focal_length=0.035,
                  sensor_height=0.024, aperture=22.0, exposure=1.0):
     """OrbitCameraComponent::Setup + CameraRenderProxy::{Update,OnTransformDirty}
-    (OrbitCameraComponent.cpp:16-30, CameraComponent.cpp:120-128, CameraRenderProxy.cpp:21-33,113-136) -> SpkCamera."""
-    rx, rz = math.radians(-pitch), math.radians(-yaw)
-    Rz = np.array([[math.cos(rz), -math.sin(rz), 0], [math.sin(rz), math.cos(rz), 0], [0, 0, 1]])
-    Rx = np.array([[1, 0, 0], [0, math.cos(rx), -math.sin(rx)], [0, math.sin(rx), math.cos(rx)]])
-    rot = Rz @ Rx
-    front = rot @ np.array([0.0, 1.0, 0.0])
-    position = front * -radius + np.asarray(center, np.float64)
-    # node rotation = Rx(pitch) * Rz(yaw) = rot^T; rows of that matrix are right/front/up
-    R = rot.T
-    right, front_r, up = R[0], R[1], R[2]
-    vfov = 2.0 * math.atan(sensor_height / (2.0 * focal_length))
-    focus = radius
-    h = math.tan(vfov / 2.0)
-    fh = 2.0 * h * focus
-    fw = (width / height) * fh
-    max_u = right * fw
-    max_v = up * fh
-    lower_left = position + front_r * focus - max_u * 0.5 - max_v * 0.5
+    (OrbitCameraComponent.cpp:16-30, CameraComponent.cpp:120-128, CameraRenderProxy.cpp:21-33,113-136) -> SpkCamera, by
+    the host library in the reference's float operation order (sparkle_b200/host/ref_math.cpp)."""
     cam = A.Camera()
-    for name, v in (("position", position), ("up", up), ("front", front_r), ("right", right), ("max_u", max_u),
-                    ("max_v", max_v), ("lower_left", lower_left)):
-        getattr(cam, name)[:] = [float(f32(x)) for x in v]
-    cam.aperture_radius = float(f32(focal_length / aperture * 0.5))
-    cam.exposure = exposure
+    c = np.ascontiguousarray(center, f32)
+    A.host_lib().spk_host_orbit_camera(c.ctypes.data_as(A.fp), radius, pitch, yaw, focal_length, sensor_height, aperture,
+                                       exposure, width, height, C.byref(cam))
     return cam

@@ -24,6 +24,8 @@ def main():
     orc = O.Oracle("reference")
     assert orc.kind == "reference"
     out = G.evaluate(orc)
+    # the reference's scene-graph float math (Transform, glTF node, orbit camera): pins the product's host/ref_math.cpp
+    out.update(G.evaluate_host_math(orc.kat_transform, orc.kat_gltf_node, orc.kat_camera))
     path = os.path.join(HERE, "reference_vectors.npz")
     np.savez_compressed(path, **out)
     print(f"wrote {path}: {len(out)} arrays, {os.path.getsize(path) / 1024:.0f} KiB")

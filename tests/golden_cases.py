@@ -95,6 +95,72 @@ def kat_surface_inputs(n=96, seed=8):
     return d, normal, tangent, uv
 
 
+def camera_floats(cam):
+    """SpkCamera as its 23 floats"""
+    return np.frombuffer(bytes(cam), np.float32).copy()
+
+
+def host_math_inputs(n=256, seed=91):
+    """seeded TRS / glTF-node / orbit-camera parameters behind the hostmath_* golden arrays (all float32-exact)"""
+    g = np.random.default_rng(seed)
+    f = np.float32
+    trs_in = np.concatenate([g.uniform(-20, 20, (n, 3)), g.uniform(-3.2, 3.2, (n, 3)), g.uniform(0.1, 5, (n, 3))], 1).astype(f)
+    trs_in[::4, 7:9] = trs_in[::4, 6:7]   # uniform scales
+    trs_in[::7, 3] = 0                     # axis-aligned rotations
+    trs_in[0, 3:6] = 0
+    trs_in[1] = [0, 0, -0.001, 0, 0, 0, 50, 50, 0.001]  # TestScene floor (UsdRoundTripTest.cpp:40-45)
+    node_in = np.concatenate([g.uniform(-20, 20, (n, 3)), g.normal(size=(n, 4))], 1).astype(f)
+    node_in[::3, 3:] /= np.linalg.norm(node_in[::3, 3:], axis=1, keepdims=True)
+    node_in[0, 3:] = [0, 0, 0, 1]
+    cam_in = np.stack([g.uniform(-5, 5, n), g.uniform(-5, 5, n), g.uniform(-5, 5, n), g.uniform(1, 60, n),
+                       g.uniform(-89, 89, n), g.uniform(-180, 180, n), g.uniform(0.015, 0.08, n), np.full(n, 0.024),
+                       g.uniform(1, 22, n), np.ones(n), g.integers(16, 4000, n), g.integers(16, 2200, n)], 1).astype(f)
+    cam_in[0] = [0, 0, 0, 25, 10, -20, 0.035, 0.024, 22, 1, 1920, 1080]  # TestScene camera (UsdRoundTripTest.cpp:28-33)
+    cam_in[1] = [0, 0, 0, 25, 10, -20, 0.035, 0.024, 22, 1, 1280, 720]
+    return trs_in, node_in, cam_in
+
+
+def evaluate_host_math(fn_trs, fn_node, fn_camera):
+    """fn_trs(t, e, s) -> (fwd, inv); fn_node(t, q) -> (fwd, inv); fn_camera(w, h, **kw) -> SpkCamera. Evaluated on the
+    reference (orc.kat_*) for the golden file and on the product's host library in tests/test_host_cpu.py."""
+    trs_in, node_in, cam_in = host_math_inputs()
+    out = {}
+    r = [fn_trs(x[0:3], x[3:6], x[6:9]) for x in trs_in]
+    out["hostmath_trs_fwd"] = np.stack([a for a, _ in r]).astype(np.float32)
+    out["hostmath_trs_inv"] = np.stack([b for _, b in r]).astype(np.float32)
+    r = [fn_node(x[0:3], x[3:7]) for x in node_in]
+    out["hostmath_node_fwd"] = np.stack([a for a, _ in r]).astype(np.float32)
+    out["hostmath_node_inv"] = np.stack([b for _, b in r]).astype(np.float32)
+    out["hostmath_camera"] = np.stack([camera_floats(fn_camera(
+        int(x[10]), int(x[11]), center=tuple(float(v) for v in x[0:3]), radius=float(x[3]), pitch=float(x[4]),
+        yaw=float(x[5]), focal_length=float(x[6]), sensor_height=float(x[7]), aperture=float(x[8]),
+        exposure=float(x[9]))) for x in cam_in])
+    return out
+
+
+def sky_scene():
+    """TestScene under a seeded RGBA16F cube-map sky (a14 with has_map, SkyRenderProxy.cpp:50-57, Image.cpp:298-357)"""
+    sb, cam = scenes.testscene()
+    g = np.random.default_rng(14)
+    faces = []
+    for f in range(6):
+        y, x = np.mgrid[0:32, 0:32] / 31.0
+        base = np.stack([0.3 + 0.7 * x, 0.2 + 0.8 * y, 0.5 + 0.5 * np.sin(6.0 * (x + y) + f), np.ones_like(x)], -1)
+        faces.append((base * (0.6 + 0.25 * f) + g.uniform(0, 0.3, base.shape)).astype(np.float16))
+    sb.set_sky(color=(0.5, 0.7, 1.0), faces=faces, fmt=A.FMT_RGBA16F)
+    return sb, cam
+
+
+WRAP_W, WRAP_H, WRAP_FRAME = 3840, 2160, 517  # C4's frame: p + 517*W*H crosses 2^32 at pixel 6,762,496 (SURVEY H6)
+
+
+def wrap_probe_pixels():
+    """pixels on either side of the 32-bit seed wrap of frame 517 at 3840x2160 (and the two neighbours of the crossing)"""
+    cross = (1 << 32) - WRAP_FRAME * WRAP_W * WRAP_H
+    ps = [0, 12345, cross - 2, cross - 1, cross, cross + 1, cross + 4321, WRAP_W * WRAP_H - 1]
+    return [(p % WRAP_W, p // WRAP_W) for p in ps]
+
+
 def evaluate(orc):
     """all golden quantities from one oracle -> dict of numpy arrays (floats kept as float32: compare the bits)"""
     out = {}
@@ -137,4 +203,13 @@ def evaluate(orc):
                                  threads=4)
             out["testscene_running_average"] = ra
             out["testscene_tonemap_f16"] = orc.resolve(acc, A.RESOLVE_TONEMAP_F16, IMG_SPP, exposure=1.25).view(np.uint16)
+            # H6: single pixel samples of C4's frame 517 at 3840x2160, seeds on both sides of the 2^32 wrap
+            cam4k = orbit_camera(WRAP_W, WRAP_H, **camkw)
+            out["testscene_wrap_samples"] = np.stack([orc.sample_pixel(desc, cam4k, WRAP_W, WRAP_H, i, j, WRAP_FRAME)[:4]
+                                                      for (i, j) in wrap_probe_pixels()])
+    # a14 with a cube map: image of TestScene under a seeded RGBA16F cube sky
+    sb, camkw = sky_scene()
+    desc = sb.finalize()
+    acc, _ = orc.render(desc, orbit_camera(IMG_W, IMG_H, **camkw), IMG_W, IMG_H, 1, IMG_SPP, max_bounce=8, threads=4)
+    out["skyscene_accum"] = acc
     return out

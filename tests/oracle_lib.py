@@ -52,6 +52,12 @@ def load(kind="reference"):
     lib.orc_sample_pixel.argtypes = [C.POINTER(A.SceneDesc), C.POINTER(A.Camera), u32, u32, u32, u32, u32, u32, f32,
                                      u32, fp, C.POINTER(OrcCounters)]
     lib.orc_resolve.argtypes = [fp, u32, u32, u32, u32, u32, f32, C.c_void_p]
+    if kind == "reference":  # KATs of the reference's scene-graph math (pin the product's host/ref_math.cpp)
+        lib.orc_kat_transform.argtypes = [fp, fp, fp, fp, fp]
+        lib.orc_kat_gltf_node.argtypes = [fp, fp, fp, fp]
+        lib.orc_kat_camera.argtypes = [fp, f32, f32, f32, f32, f32, f32, f32, u32, u32, C.POINTER(A.Camera)]
+    else:
+        lib.orc_set_libm.argtypes = [u32]
     _cache[kind] = lib
     return lib
 
@@ -92,9 +98,35 @@ class Oracle:
             raise RuntimeError(f"orc_sample_pixel -> {rc}")
         return out
 
+    def set_libm(self, device_libm):
+        """port only: False = glibc float sin/cos/pow like the reference (default); True = double, rounded once, like
+        the CUDA path. Process-wide: reset it in a finally block."""
+        assert self.kind == "port"
+        self.lib.orc_set_libm(1 if device_libm else 0)
+
+    def kat_transform(self, translate, euler, scale):
+        t, e, s = (np.ascontiguousarray(v, np.float32) for v in (translate, euler, scale))
+        fwd, inv = np.zeros(12, np.float32), np.zeros(12, np.float32)
+        self.lib.orc_kat_transform(*[a.ctypes.data_as(A.fp) for a in (t, e, s, fwd, inv)])
+        return fwd.reshape(3, 4), inv.reshape(3, 4)
+
+    def kat_gltf_node(self, translation, rotation_xyzw):
+        t, q = np.ascontiguousarray(translation, np.float32), np.ascontiguousarray(rotation_xyzw, np.float32)
+        fwd, inv = np.zeros(12, np.float32), np.zeros(12, np.float32)
+        self.lib.orc_kat_gltf_node(*[a.ctypes.data_as(A.fp) for a in (t, q, fwd, inv)])
+        return fwd.reshape(3, 4), inv.reshape(3, 4)
+
+    def kat_camera(self, width, height, center=(0, 0, 0), radius=25.0, pitch=10.0, yaw=-20.0, focal_length=0.035,
+                   sensor_height=0.024, aperture=22.0, exposure=1.0):
+        cam = A.Camera()
+        c = np.ascontiguousarray(center, np.float32)
+        self.lib.orc_kat_camera(c.ctypes.data_as(A.fp), radius, pitch, yaw, focal_length, sensor_height, aperture,
+                                exposure, width, height, C.byref(cam))
+        return cam
+
     def resolve(self, accum, fmt, total_samples, exposure=1.0, accum_mode=A.ACCUM_SUM):
         h, w = accum.shape[:2]
-        out = np.empty((h, w, 4), np.float32 if fmt == A.RESOLVE_LINEAR_F32 else np.float16)
+        out = np.empty((h, w, 4), {A.RESOLVE_LINEAR_F32: np.float32, A.RESOLVE_TONEMAP_F16: np.float16}.get(fmt, np.uint8))
         rc = self.lib.orc_resolve(np.ascontiguousarray(accum).ctypes.data_as(A.fp), w, h, accum_mode, fmt,
                                   total_samples, exposure, out.ctypes.data)
         if rc != 0:

@@ -98,3 +98,38 @@ def test_malformed_files_fail_loudly(tmp_path):
     assert not lib.spk_host_scene_load_gltf(str(bad).encode(), 0)
     with pytest.raises(RuntimeError):
         app.gltf_probe(bad)
+
+
+def test_hand_written_fixture_world_positions():
+    """tests/golden/hand_triangle.gltf is written by hand (not by gltf_export.py), and the expected world positions are
+    derived by hand from the reference's rules, so a sign error shared by the exporter and the loader cannot cancel:
+      LoadPositionArray (GLTFLoader.cpp:192-247)  node.scale is baked into the vertices: v * (2, 3, 4)
+      ProcessNode (GLTFLoader.cpp:532-544)        rotation = Rx(+90 deg) * node.rotation; translation used as it is
+    node 0: rotation = 90 deg about glTF +Y: (x, y, z) -> (z, y, -x); then Rx(+90): (x, y, z) -> (x, -z, y); + (10, 20, 30)
+      (1,0,0) -> (2,0,0) -> (0,0,-2) -> (0, 2,0) -> (10,22,30)
+      (0,1,0) -> (0,3,0) -> (0,3, 0) -> (0, 0,3) -> (10,20,33)
+      (0,0,1) -> (0,0,4) -> (4,0, 0) -> (4, 0,0) -> (14,20,30)
+    node 1 (no TRS): only the y-up -> z-up rotation: (1,0,0) -> (1,0,0), (0,1,0) -> (0,0,1), (0,0,1) -> (0,-1,0)"""
+    lib = A.host_lib()
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "hand_triangle.gltf")
+    h = lib.spk_host_scene_load_gltf(path.encode(), 0)
+    assert h, lib.spk_host_last_error().decode()
+    d = lib.spk_host_scene_desc(h).contents
+    assert d.num_primitives == 2 and d.num_meshes == 2  # scale differs: the two nodes cannot share a BLAS
+    want = [np.array([[10, 22, 30], [10, 20, 33], [14, 20, 30]], np.float64),
+            np.array([[1, 0, 0], [0, 0, 1], [0, -1, 0]], np.float64)]
+    baked = [np.diag([2.0, 3.0, 4.0]), np.eye(3)]
+    for p in range(2):
+        pd = d.primitives[p]
+        md = d.meshes[pd.mesh]
+        v = np.ctypeslib.as_array(md.vertices, (md.num_vertices, 3)).astype(np.float64)
+        assert np.array_equal(v, baked[p]), "node.scale baked into the vertices, and only there"
+        fwd = np.array(pd.fwd[:], np.float64).reshape(3, 4)
+        inv = np.array(pd.inv[:], np.float64).reshape(3, 4)
+        world = v @ fwd[:, :3].T + fwd[:, 3]
+        assert np.allclose(world, want[p], atol=1e-5), (p, world)
+        assert np.allclose(world @ inv[:, :3].T + inv[:, 3], v, atol=1e-5)
+        assert np.allclose(np.linalg.norm(fwd[:, :3], axis=0), 1.0, atol=1e-6), "the node keeps scale 1"
+        idx = np.ctypeslib.as_array(md.indices, (3,))
+        assert idx.tolist() == [0, 1, 2]
+    lib.spk_host_scene_free(h)

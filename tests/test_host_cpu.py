@@ -1,12 +1,58 @@
 """CPU tests of the host side (no GPU): the BVH builder's invariants, the `pipeline` switch (Str2Enum semantics of
 core/Enum.h:20-32 and the new `cuda` enumerator), the no-fallback rule of Renderer::CreateRenderer, and the C++
 TestScene recipe against the Python one."""
+import os
+
 import numpy as np
 import pytest
 
+import golden_cases as G
+import oracle_lib as O
 from sparkle_b200 import _abi as A
 from sparkle_b200 import app, geometry, scenes
-from sparkle_b200.scene import HostBvh
+from sparkle_b200.scene import HostBvh, orbit_camera
+
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.npz")
+
+
+def host_trs(t, e, s):
+    return geometry.trs(t, e, s)
+
+
+def host_node(t, q):
+    t, q = np.ascontiguousarray(t, np.float32), np.ascontiguousarray(q, np.float32)
+    fwd, inv = np.empty(12, np.float32), np.empty(12, np.float32)
+    A.host_lib().spk_host_gltf_node(*[a.ctypes.data_as(A.fp) for a in (t, q, fwd, inv)])
+    return fwd.reshape(3, 4), inv.reshape(3, 4)
+
+
+def test_host_math_reproduces_the_reference_bit_for_bit():
+    """a17 + transforms: the product's Transform / glTF-node / orbit-camera math (host/ref_math.cpp, used by both the C++
+    host and these Python bindings) against the reference's OWN Transform::UpdateTransformData (Transform.cpp:52-64) and
+    CameraRenderProxy::OnTransformDirty (CameraRenderProxy.cpp:113-136), via the committed golden vectors
+    (hostmath_*, generated from oracle/_ref by tests/golden/make_golden.py) and, where the reference library is
+    built, live on a larger seeded set. Same float32 VALUES everywhere (-0 == +0)."""
+    golden = dict(np.load(GOLDEN))
+    got = G.evaluate_host_math(host_trs, host_node, orbit_camera)
+    for k, v in got.items():
+        assert v.dtype == np.float32 and np.array_equal(v, golden[k]), f"{k}: {int((v != golden[k]).sum())} values differ"
+    if not O.available("reference"):
+        return
+    ref = O.Oracle("reference")
+    g = np.random.default_rng(2024)
+    for _ in range(3000):
+        t, e, s = g.uniform(-50, 50, 3), g.uniform(-6.3, 6.3, 3), g.uniform(0.05, 20, 3)
+        a, b = host_trs(t, e, s), ref.kat_transform(t, e, s)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (t, e, s)
+        q = g.normal(size=4)
+        a, b = host_node(t, q), ref.kat_gltf_node(t, q)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (t, q)
+        kw = dict(center=tuple(g.uniform(-9, 9, 3)), radius=float(g.uniform(0.5, 90)), pitch=float(g.uniform(-89, 89)),
+                  yaw=float(g.uniform(-180, 180)), focal_length=float(g.uniform(0.01, 0.1)),
+                  aperture=float(g.uniform(0.95, 22)))
+        w, h = int(g.integers(2, 4096)), int(g.integers(2, 2304))
+        assert np.array_equal(G.camera_floats(orbit_camera(w, h, **kw)), G.camera_floats(ref.kat_camera(w, h, **kw))), kw
 
 
 def _has_gpu():
