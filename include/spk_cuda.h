@@ -3,7 +3,7 @@
  *
  * This is the drop-in boundary. The reference has no FFI: its renderers are C++
  * classes behind `Renderer::CreateRenderer` (libraries/source/renderer/renderer/Renderer.cpp:17-53).
- * A `CudaRenderer : Renderer` (see sparkle_b200/host/renderer.h and INTEGRATION.md) binds exactly the
+ * A `CudaRenderer : Renderer` (see sparkle_b200/host/cuda_renderer.h and INTEGRATION.md) binds exactly the
  * entry points below. Plain pointers and sizes only; no C++ / torch types cross this line.
  *
  * Conventions
@@ -190,7 +190,9 @@ typedef struct SpkRenderParams {
     float output_limit;     /* CameraRenderProxy::OutputLimit (6) */
     uint32_t accum_mode;    /* SpkAccumMode */
     uint32_t flags;
-    uint32_t pad;
+    uint32_t cumulated_cap; /* running average only: the moving-average weight uses min(cumulated, cap) samples, the
+                               camera's cumulated count capped at max_spp (CameraRenderProxy.cpp:70-73): past the cap
+                               the reference's frame buffer becomes an exponential moving average. 0 = no cap */
 } SpkRenderParams;
 
 /* 32-byte ray, 20-byte hit (IntersectionCandidate, Intersection.h:91-104). */
@@ -277,6 +279,21 @@ int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_ray
 /* Same with device-resident buffers (no copies); asynchronous on the context stream. */
 int spk_cuda_trace_closest_device(SpkContext *ctx, const void *d_rays, uint64_t num_rays, void *d_hits,
                                   uint32_t flags);
+
+/* Tuning knobs, explicit (nothing in the library reads the environment). Defaults are the measured choices. */
+typedef enum SpkOption {
+    SPK_OPT_MEGAKERNEL_FORM = 0, /* 0 = measured choice (spk_cuda_choose_tracer; 2162 until measured). Forms: 2162 / 2084
+                                    persistent pixel-pulling sorted megakernel, 16 warps x 2 / 8 warps x 4 CTAs per SM;
+                                    1162 / 1084 / 1083 the same with pixels owned by a CTA (round-1 form); 831 / 830 /
+                                    1621 / 461 phased kernel; 1 = plain per-pixel loop */
+    SPK_OPT_WAVEFRONT_SLOTS = 1, /* path slots of the wavefront tracer (default 2^24; 100 bytes each) */
+    SPK_OPT_WAVEFRONT_CHUNK = 2, /* wavefront iterations queued per host read of the control block (default 8) */
+    SPK_OPT_TRACE_VOTE = 3,      /* ray-batch kernel: lanes waiting in a leaf state that switch the warp to it (4, 6, 8, 12, 16; default 6) */
+    SPK_OPT_SMEM_CARVEOUT = 4,   /* percent of the SM's shared-memory/L1 array asked for as shared memory; -1 driver
+                                    default, -2 (default) the smallest that holds the resident CTAs */
+    SPK_OPT_VERBOSE = 5          /* 1: spk_cuda_choose_tracer prints its timings to stderr */
+} SpkOption;
+int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value);
 
 int spk_cuda_get_stats(SpkContext *ctx, SpkStats *out);
 int spk_cuda_reset_stats(SpkContext *ctx);

@@ -1388,7 +1388,9 @@ int orc_render(const SpkSceneDesc *scene, const SpkCamera *camera, uint32_t widt
         if (params->accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
         {
             // DenoisePass, temporal part (CPURenderer.cpp:526-544): acc = Lerp(new, acc, N / (N + spp)), spp = 1
-            float ma = static_cast<float>(*cumulated) / static_cast<float>(*cumulated + 1u);
+            // CameraRenderProxy::Update caps the cumulated count at max_spp (CameraRenderProxy.cpp:70-73)
+            const uint32_t capped = params->cumulated_cap ? std::min(*cumulated, params->cumulated_cap) : *cumulated;
+            float ma = static_cast<float>(capped) / static_cast<float>(capped + 1u);
             for (size_t k = 0; k < frame.size(); k++)
             {
                 accum[k] = lerp1(frame[k], accum[k], ma);

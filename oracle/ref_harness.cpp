@@ -828,7 +828,9 @@ int orc_render(const SpkSceneDesc *scene, const SpkCamera *camera, uint32_t widt
         renderer.BasePass(*rs->scene, cfg, no_debug);
         if (params->accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
         {
-            rs->camera->cumulated_sample_count_ = *cumulated;
+            // the cap CameraRenderProxy::Update applies (CameraRenderProxy.cpp:70-73; Update itself needs the RHI)
+            rs->camera->cumulated_sample_count_ =
+                params->cumulated_cap ? std::min(*cumulated, params->cumulated_cap) : *cumulated;
             renderer.DenoisePass(cfg, no_debug); // spatial_denoise=false: temporal lerp only (CPURenderer.cpp:530-544)
         }
         else

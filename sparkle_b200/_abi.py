@@ -17,6 +17,8 @@ ACCUM_SUM, ACCUM_RUNNING_AVERAGE = 0, 1
 FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY, FLAG_AUTO_TRACER = 1, 2, 4, 8, 16
 FLAG_SPATIAL_DENOISE = 32
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
+(OPT_MEGAKERNEL_FORM, OPT_WAVEFRONT_SLOTS, OPT_WAVEFRONT_CHUNK, OPT_TRACE_VOTE, OPT_SMEM_CARVEOUT,
+ OPT_VERBOSE) = range(6)
 
 u32, i32, f32, u64 = C.c_uint32, C.c_int32, C.c_float, C.c_uint64
 fp = C.POINTER(f32)
@@ -70,7 +72,7 @@ class Camera(C.Structure):
 
 class RenderParams(C.Structure):
     _fields_ = [("first_sample", u32), ("sample_count", u32), ("sample_stride", u32), ("max_bounce", u32),
-                ("output_limit", f32), ("accum_mode", u32), ("flags", u32), ("pad", u32)]
+                ("output_limit", f32), ("accum_mode", u32), ("flags", u32), ("cumulated_cap", u32)]
 
 
 class Ray(C.Structure):
@@ -99,6 +101,7 @@ CUDA_SYMBOLS = {
     "spk_cuda_create": (C.c_int, [C.POINTER(CreateInfo), C.POINTER(CtxP)]),
     "spk_cuda_destroy": (C.c_int, [CtxP]),
     "spk_cuda_set_stream": (C.c_int, [CtxP, C.c_void_p]),
+    "spk_cuda_set_option": (C.c_int, [CtxP, u32, C.c_int64]),
     "spk_cuda_upload_scene": (C.c_int, [CtxP, C.POINTER(SceneDesc)]),
     "spk_cuda_update_instances": (C.c_int, [CtxP, C.POINTER(PrimitiveDesc), u32, C.POINTER(BvhDesc)]),
     "spk_cuda_set_camera": (C.c_int, [CtxP, C.POINTER(Camera)]),

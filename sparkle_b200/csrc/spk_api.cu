@@ -326,6 +326,57 @@ int spk_cuda_destroy(SpkContext *ctx)
     return SPK_OK;
 }
 
+int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value)
+{
+    if (!ctx)
+    {
+        return invalid("null context");
+    }
+    switch (option)
+    {
+    case SPK_OPT_MEGAKERNEL_FORM:
+        if (value < 0 || value > 9999)
+        {
+            return invalid("spk_cuda_set_option: megakernel form");
+        }
+        ctx->opt_mega_form = int(value);
+        return SPK_OK;
+    case SPK_OPT_WAVEFRONT_SLOTS:
+        if (value < 32 || value > (int64_t(1) << 28))
+        {
+            return invalid("spk_cuda_set_option: wavefront slots must be in [32, 2^28]");
+        }
+        ctx->opt_wf_slots = uint32_t(value);
+        return SPK_OK;
+    case SPK_OPT_WAVEFRONT_CHUNK:
+        if (value < 1 || value > 1024)
+        {
+            return invalid("spk_cuda_set_option: wavefront chunk must be in [1, 1024]");
+        }
+        ctx->opt_wf_chunk = uint32_t(value);
+        return SPK_OK;
+    case SPK_OPT_TRACE_VOTE:
+        if (value != 4 && value != 6 && value != 8 && value != 12 && value != 16)
+        {
+            return invalid("spk_cuda_set_option: vote must be 4, 6, 8, 12 or 16");
+        }
+        ctx->opt_vote = int(value);
+        return SPK_OK;
+    case SPK_OPT_SMEM_CARVEOUT:
+        if (value < -2 || value > 100)
+        {
+            return invalid("spk_cuda_set_option: carve-out percent");
+        }
+        ctx->opt_carveout = int(value);
+        return SPK_OK;
+    case SPK_OPT_VERBOSE:
+        ctx->opt_verbose = value != 0;
+        return SPK_OK;
+    default:
+        return invalid("spk_cuda_set_option: unknown option");
+    }
+}
+
 int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream)
 {
     if (!ctx)
@@ -639,10 +690,10 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
     }
     for (uint32_t p = 0; p < num_primitives; p++)
     {
-        if (primitives[p].kind > SPK_PRIM_SPHERE ||
+        if (primitives[p].kind > SPK_PRIM_SPHERE || primitives[p].material >= ctx->material_class.size() ||
             (primitives[p].kind == SPK_PRIM_MESH && primitives[p].mesh >= ctx->mesh_root_word.size()))
         {
-            return invalid("spk_cuda_update_instances: primitive references a missing mesh");
+            return invalid("spk_cuda_update_instances: primitive references a missing mesh or material");
         }
     }
     SPK_CUDA_TRY(cudaSetDevice(ctx->device));
@@ -663,6 +714,18 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
                                  cudaMemcpyHostToDevice, ctx->stream));
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->scene.tlas_root = root_word(*tlas, ctx->tlas_pair_base, 0);
+    // the t-culling slack is sized from the world extent (spk_traverse.cuh): primitives may have moved outside the
+    // bounds of the upload, so take it again from the rebuilt TLAS root (= the world AABB)
+    const HostNode root = read_node(*tlas, 0);
+    float extent = 0.f;
+    for (float b : root.bounds)
+    {
+        extent = std::max(extent, std::fabs(b));
+    }
+    if (extent > 0.f && std::isfinite(extent))
+    {
+        ctx->scene.cull_extent = extent;
+    }
     return SPK_OK;
 }
 

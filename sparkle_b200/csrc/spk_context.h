@@ -51,7 +51,14 @@ struct SpkContext
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
     void *wf_block = nullptr;
     uint32_t wf_slots = 0;
-    int mega_variant = 1162; // megakernel form (SPK_RENDER_PHASED code) spk_cuda_choose_tracer measured fastest
+    int mega_variant = 2162; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
+    // explicit options (spk_cuda_set_option); nothing is read from the environment
+    int opt_mega_form = 0;           // 0: use mega_variant
+    uint32_t opt_wf_slots = 1u << 24; // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
+    uint32_t opt_wf_chunk = 8;
+    int opt_vote = 6;
+    int opt_carveout = -2;
+    bool opt_verbose = false;
     int tracer_choice = -1; // -1 not measured for this scene, 0 megakernel, 1 wavefront (spk_cuda_choose_tracer)
 };
 
@@ -70,14 +77,15 @@ int cuda_fail(cudaError_t e, const char *what);
 // Shared memory and L1 split one 256 KB array per SM. Asks for the smallest carve-out that still holds `ctas` resident
 // CTAs of `bytes_per_cta` (+1 KB the driver reserves per CTA), so that the rest serves the BVH as L1: the default
 // heuristic leaves the traversal kernels ~32 KB less L1 than they can have (measured: DESIGN.md 4.2).
-template <class Kernel> cudaError_t prefer_small_carveout(Kernel kernel, size_t bytes_per_cta, int ctas)
+template <class Kernel>
+cudaError_t prefer_small_carveout(Kernel kernel, size_t bytes_per_cta, int ctas, int override_pct = -2)
 {
     const size_t pool = 228 * 1024;
     int pct = int((size_t(ctas) * (bytes_per_cta + 1024) * 100 + pool - 1) / pool);
-    if (const char *e = getenv("SPK_CARVEOUT"))
-        pct = atoi(e);
+    if (override_pct != -2)
+        pct = override_pct; // SPK_OPT_SMEM_CARVEOUT
     if (pct < 0)
-        return cudaSuccess; // SPK_CARVEOUT=-1: the driver's default
+        return cudaSuccess; // -1: the driver's default
     return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
 }
 

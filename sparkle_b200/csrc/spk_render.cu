@@ -16,6 +16,7 @@
  */
 #include "spk_context.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include "spk_shade.cuh"
@@ -36,6 +37,7 @@ struct RenderArgs
     uint32_t accum_mode;
     uint32_t debug;
     uint32_t cumulated; // samples already in the accumulator (running-average mode)
+    uint32_t cumulated_cap; // the camera's cap on that count (max_spp, CameraRenderProxy.cpp:70-73); 0xFFFFFFFF none
 };
 
 // GBUF: one sample per pixel into a g-buffer instead of the accumulator (RenderPixel with spatial_denoise,
@@ -141,7 +143,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
             }
             else if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
             {
-                uint32_t n = a.cumulated + s;
+                uint32_t n = min(a.cumulated + s, a.cumulated_cap);
                 float ma = (float)n / (float)(n + 1u);
                 acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
                                   lerp1(valid, acc.w, ma));
@@ -336,7 +338,7 @@ need_path = false;
                     color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
                     if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
                     {
-                        uint32_t n = a.cumulated + s;
+                        uint32_t n = min(a.cumulated + s, a.cumulated_cap);
                         float ma = (float)n / (float)(n + 1u);
                         acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
                                           lerp1(valid, acc.w, ma));
@@ -392,7 +394,15 @@ template <int WARPS> constexpr size_t sorted_smem_bytes()
 // warp_trace_loop, lanes refilling from a shared-memory cursor). With only 256 rays per phase the loop's start-up, votes
 // and drain cost more than the idle lanes they save: TestScene 36.5 vs 23.4 ms per 32 spp, city 415 vs 327, room 233 vs
 // 159 (B200, same launch shapes).
-template <bool CULL, bool COUNT, int WARPS, int MINB>
+// PULL (the shipped form): the grid is persistent (SM count x CTAs per SM) and a column is not tied to a pixel. When a
+// column's pixel has all its samples the thread that shaded its last segment writes the pixel's sum to the accumulation
+// buffer and takes the NEXT PIXEL from a global counter (tile-linear order: 32 consecutive indices are one 8x4 tile), so
+// columns stay busy until the image is exhausted. Without it a CTA owned 512 pixels and lived until its SLOWEST pixel
+// had finished its samples (a pixel on glass needs up to 8x the segments of a sky pixel), holding its half of the SM's
+// threads and shared memory with a few live columns. A pixel's samples are still added in order by one thread at a
+// time, so the image is bit-identical to the owner forms. The column's pixel index lives in 16 bits of shared memory
+// plus 7 bits of the packed word (sample : 17 | pixel_hi : 7 | bounce : 8): < 2^23 pixels, < 2^17 samples per call.
+template <bool CULL, bool COUNT, int WARPS, int MINB, bool PULL>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
     render_sorted_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
                          unsigned long long *__restrict__ counters)
@@ -403,18 +413,62 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     __shared__ uint32_t s_bin[2][32];
     __shared__ uint32_t s_total;
     __shared__ uint16_t s_sorted[T];
+    __shared__ uint16_t s_pixel_lo[PULL ? T : 1];
     const uint32_t tid = threadIdx.x;
     const uint32_t tiles_x = (a.width + kTileW - 1) / kTileW;
     const uint32_t lane = tid & 31;
+    constexpr uint32_t kSampleShift = PULL ? 15u : 8u; // packed word: sample above, (pixel_hi,) bounce below
     // column c of the CTA <-> pixel: a warp-sized run of columns is one 8x4 tile
     auto pixel_of = [&](uint32_t c, uint32_t &pi, uint32_t &pj) {
         const uint32_t w = blockIdx.x * WARPS + (c >> 5), l = c & 31u;
         pi = (w % tiles_x) * kTileW + (l & (kTileW - 1));
         pj = (w / tiles_x) * kTileH + (l / kTileW);
     };
-    uint32_t i, j;
-    pixel_of(tid, i, j);
-    const bool in_image = i < a.width && j < a.height;
+    // PULL: tile-linear pixel index <-> pixel
+    auto pixel_of_index = [&](uint32_t p, uint32_t &pi, uint32_t &pj) {
+        const uint32_t w = p >> 5, l = p & 31u;
+        pi = (w % tiles_x) * kTileW + (l & (kTileW - 1));
+        pj = (w / tiles_x) * kTileH + (l / kTileW);
+    };
+    const uint32_t total_px = tiles_x * ((a.height + kTileH - 1) / kTileH) * 32u;
+    unsigned int *next_pixel = reinterpret_cast<unsigned int *>(counters + 7);
+    uint32_t i = 0, j = 0;
+    bool in_image;
+    uint32_t pixels_done = 0;
+    if (PULL)
+    {
+        // one atomic per warp: the warp's first 32 pixels are one tile (coherent camera rays, like the owner forms)
+        uint32_t p = 0;
+        in_image = false;
+        for (;;)
+        {
+            if (lane == 0)
+            {
+                p = atomicAdd(next_pixel, 32u);
+            }
+            p = __shfl_sync(0xffffffffu, p, 0) + lane;
+            if (p - lane >= total_px)
+            {
+                break;
+            }
+            pixel_of_index(p, i, j);
+            in_image = i < a.width && j < a.height;
+            if (__any_sync(0xffffffffu, in_image))
+            {
+                break;
+            }
+        }
+        if (in_image)
+        {
+            s_pixel_lo[tid] = (uint16_t)p;
+            s_state[tid + 18 * T] = __uint_as_float((p >> 16) << 8); // pixel_hi; start_path keeps it
+        }
+    }
+    else
+    {
+        pixel_of(tid, i, j);
+        in_image = i < a.width && j < a.height;
+    }
     uint32_t rays = 0;
     TraceCounters cnt{0, 0, 0, 0};
     const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
@@ -456,7 +510,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
         c[10 * T] = __uint_as_float(rng.s1);
         c[11 * T] = __uint_as_float(rng.s2);
         c[12 * T] = __uint_as_float(rng.s3);
-        c[18 * T] = __uint_as_float(sample << 8); // sample index : 24 | bounce : 8
+        // sample index | (PULL: the column's pixel_hi, kept) | bounce = 0
+        c[18 * T] = __uint_as_float((sample << kSampleShift) | (PULL ? (__float_as_uint(c[18 * T]) & 0x7F00u) : 0u));
     };
     float *mine = s_state + tid; // the column this thread works on in the current iteration
     bool have = in_image && a.sample_count > 0u;
@@ -543,7 +598,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             h.inst = __float_as_uint(src[16 * T]);
             h.face = __float_as_uint(src[17 * T]);
             const uint32_t packed = __float_as_uint(src[18 * T]);
-            const uint32_t sample = packed >> 8;
+            const uint32_t sample = packed >> kSampleShift;
             uint32_t b = packed & 255u;
             V3 color = mk(0.f, 0.f, 0.f);
             float valid = 1.f;
@@ -614,7 +669,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                             src[10 * T] = __uint_as_float(r.s1);
                             src[11 * T] = __uint_as_float(r.s2);
                             src[12 * T] = __uint_as_float(r.s3);
-                            src[18 * T] = __uint_as_float((sample << 8) | b);
+                            src[18 * T] = __uint_as_float((packed & ~255u) | b);
                         }
                     }
                 }
@@ -625,7 +680,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                 float4 acc = make_float4(src[19 * T], src[20 * T], src[21 * T], src[22 * T]);
                 if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
                 {
-                    uint32_t n = a.cumulated + sample;
+                    uint32_t n = min(a.cumulated + sample, a.cumulated_cap);
                     float ma = (float)n / (float)(n + 1u);
                     acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
                                       lerp1(valid, acc.w, ma));
@@ -641,8 +696,46 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                 if (sample + 1u < a.sample_count)
                 {
                     uint32_t pi, pj;
-                    pixel_of(column, pi, pj);
+                    if (PULL)
+                    {
+                        pixel_of_index((((packed >> 8) & 0x7Fu) << 16) | s_pixel_lo[column], pi, pj);
+                    }
+                    else
+                    {
+                        pixel_of(column, pi, pj);
+                    }
                     start_path(src, pi, pj, sample + 1u);
+                }
+                else if (PULL)
+                {
+                    // the pixel has all its samples: store its sum, take the next pixel of the image for this column
+                    uint32_t pi, pj;
+                    pixel_of_index((((packed >> 8) & 0x7Fu) << 16) | s_pixel_lo[column], pi, pj);
+                    accum[size_t(pj) * a.width + pi] = acc;
+                    pixels_done++;
+                    have = false;
+                    for (;;)
+                    {
+                        const uint32_t p = atomicAdd(next_pixel, 1u);
+                        if (p >= total_px)
+                        {
+                            break; // image exhausted: the column stays out of the next sort
+                        }
+                        pixel_of_index(p, pi, pj);
+                        if (pi < a.width && pj < a.height)
+                        {
+                            const float4 old = accum[size_t(pj) * a.width + pi];
+                            src[19 * T] = old.x;
+                            src[20 * T] = old.y;
+                            src[21 * T] = old.z;
+                            src[22 * T] = old.w;
+                            s_pixel_lo[column] = (uint16_t)p;
+                            src[18 * T] = __uint_as_float((p >> 16) << 8);
+                            start_path(src, pi, pj, 0u);
+                            have = true;
+                            break;
+                        }
+                    }
                 }
                 else
                 {
@@ -651,14 +744,14 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             }
         }
     }
-    if (in_image)
+    if (!PULL && in_image)
     {
         const float *own = s_state + tid;
         accum[size_t(j) * a.width + i] = make_float4(own[19 * T], own[20 * T], own[21 * T], own[22 * T]);
     }
     uint32_t total = __reduce_add_sync(0xffffffffu, rays);
-    uint32_t pixels = __popc(__ballot_sync(0xffffffffu, in_image));
-    if (lane == 0 && pixels)
+    uint32_t pixels = PULL ? __reduce_add_sync(0xffffffffu, pixels_done) : __popc(__ballot_sync(0xffffffffu, in_image));
+    if (lane == 0 && (pixels || total))
     {
         atomicAdd(counters + 0, (unsigned long long)pixels * a.sample_count);
         atomicAdd(counters + 1, (unsigned long long)total);
@@ -679,16 +772,19 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
 }
 
 // the sorted kernel's dynamic shared memory exceeds the 48 KiB default: opt in once per instantiation
-template <int W, int B> cudaError_t sorted_allow_smem()
+template <int W, int B, bool PULL> cudaError_t sorted_allow_smem(int carveout)
 {
-    static cudaError_t done = [] {
+    static cudaError_t done = [carveout] {
         cudaError_t e = cudaSuccess;
         const int bytes = (int)sorted_smem_bytes<W>();
+        // static shared memory next to it: sorted index, (PULL) pixel index, two histogram sets, the total
+        const int fixed = W * 32 * 2 * (PULL ? 2 : 1) + 2 * 32 * 4 + 16;
 #define SPK_ALLOW(C, N)                                                                                                \
     if (e == cudaSuccess)                                                                                              \
-        e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);    \
+        e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B, PULL>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                 bytes);                                                                               \
     if (e == cudaSuccess)                                                                                              \
-        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B>, bytes + W * 32 * 2 + 2 * 32 * 4 + 16, B);
+        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B, PULL>, bytes + fixed, B, carveout);
         SPK_ALLOW(true, false)
         SPK_ALLOW(false, false)
         SPK_ALLOW(true, true)
@@ -760,59 +856,75 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
     a.output_limit = p->output_limit;
     a.accum_mode = p->accum_mode;
     a.cumulated = ctx->accum_samples;
+    a.cumulated_cap = p->cumulated_cap ? p->cumulated_cap : 0xFFFFFFFFu;
     a.debug = (p->flags >> 8) & 3u;
     uint32_t tiles = ((a.width + kTileW - 1) / kTileW) * ((a.height + kTileH - 1) / kTileH);
     const DScene &scene = ctx->scene;
     const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
-    // the form of the megakernel: SPK_RENDER_PHASED forces one (A/B runs), otherwise the one spk_cuda_choose_tracer
-    // measured fastest on this scene (831 = phased, 8 warps per CTA, 3 CTAs per SM, both barriers, until measured)
-    static const int phased_setting = [] {
-        const char *e = getenv("SPK_RENDER_PHASED");
-        return e ? atoi(e) : -1;
-    }();
-    int phased = phased_setting >= 0 ? phased_setting : ctx->mega_variant;
-    // (the sorted kernel packs sample index : 24 | bounce : 8 into one word of its path slot)
+    // the form of the megakernel: SPK_OPT_MEGAKERNEL_FORM forces one (A/B runs), otherwise the one
+    // spk_cuda_choose_tracer measured fastest on this scene (2162 until measured)
+    int phased = ctx->opt_mega_form > 0 ? ctx->opt_mega_form : ctx->mega_variant;
+    const uint32_t total_px = tiles * 32u;
+    if (phased >= 2000 && (a.sample_count >= (1u << 17) || total_px >= (1u << 23)))
+    {
+        phased -= 1000; // the pulling form packs sample : 17 | pixel_hi : 7 | bounce : 8 into one word of a path slot
+    }
+    // (the owner forms pack sample index : 24 | bounce : 8)
     if (phased >= 1000 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE) && a.max_bounce != 0u && a.debug == 0u &&
         a.max_bounce <= 255u && a.sample_count < (1u << 24))
     {
-        // SPK_RENDER_PHASED = 1000 + warps*10 + min_blocks: render_sorted_kernel
-#define SPK_SORTED_CASE(W, B)                                                                                          \
-    case 1000 + W * 10 + B:                                                                                            \
-        SPK_CUDA_TRY((sorted_allow_smem<W, B>()));                                                                     \
+        static int sms = 0;
+        if (sms == 0)
+        {
+            SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+        }
+        if (phased >= 2000)
+        {
+            // the pixel counter of the pulling form (counters[7]) starts every launch at zero
+            SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), ctx->stream));
+        }
+        // form = 1000 + warps*10 + CTAs/SM: pixels owned by the CTA, one CTA per 16 tiles; 2000 + ...: persistent grid
+#define SPK_SORTED_LAUNCH(W, B, PULL, C, N)                                                                            \
+    render_sorted_kernel<C, N, W, B, PULL><<<(PULL) ? std::min<uint32_t>((tiles + W - 1) / W, uint32_t(sms) * B)       \
+                                                    : (tiles + W - 1) / W,                                             \
+                                             W * 32, sorted_smem_bytes<W>(), ctx->stream>>>(                           \
+        scene, ctx->camera, a, ctx->d_accum, ctx->d_counters)
+#define SPK_SORTED_CASE(W, B, PULL)                                                                                    \
+    case (PULL ? 2000 : 1000) + W * 10 + B:                                                                            \
+        SPK_CUDA_TRY((sorted_allow_smem<W, B, PULL>(ctx->opt_carveout)));                                              \
         if (!exact && !count)                                                                                          \
-            render_sorted_kernel<true, false, W, B>                                                                      \
-                <<<(tiles + W - 1) / W, W * 32, sorted_smem_bytes<W>()   , ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+            SPK_SORTED_LAUNCH(W, B, PULL, true, false);                                                                \
         else if (exact && !count)                                                                                      \
-            render_sorted_kernel<false, false, W, B>                                                                     \
-                <<<(tiles + W - 1) / W, W * 32, sorted_smem_bytes<W>()   , ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+            SPK_SORTED_LAUNCH(W, B, PULL, false, false);                                                               \
         else if (!exact)                                                                                               \
-            render_sorted_kernel<true, true, W, B>                                                                       \
-                <<<(tiles + W - 1) / W, W * 32, sorted_smem_bytes<W>()   , ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+            SPK_SORTED_LAUNCH(W, B, PULL, true, true);                                                                 \
         else                                                                                                           \
-            render_sorted_kernel<false, true, W, B>                                                                      \
-                <<<(tiles + W - 1) / W, W * 32, sorted_smem_bytes<W>()   , ctx->stream>>>(scene, ctx->camera, a, ctx->d_accum, ctx->d_counters); \
+            SPK_SORTED_LAUNCH(W, B, PULL, false, true);                                                                \
         break;
         switch (phased)
         {
-            SPK_SORTED_CASE(8, 3)
-            SPK_SORTED_CASE(8, 4)
-            SPK_SORTED_CASE(16, 2)
+            SPK_SORTED_CASE(8, 3, false)
+            SPK_SORTED_CASE(8, 4, false)
+            SPK_SORTED_CASE(16, 2, false)
+            SPK_SORTED_CASE(8, 4, true)
+            SPK_SORTED_CASE(16, 2, true)
         default:
-            set_error("spk_cuda_render: unknown SPK_RENDER_PHASED variant");
+            set_error("spk_cuda_render: unknown megakernel form (SPK_OPT_MEGAKERNEL_FORM)");
             return SPK_ERR_INVALID_ARGUMENT;
         }
 #undef SPK_SORTED_CASE
+#undef SPK_SORTED_LAUNCH
         SPK_CUDA_TRY(cudaGetLastError());
         ctx->stats.kernel_launches++;
         return SPK_OK;
     }
-    if (phased != 0 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE))
+    if (phased != 1 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE))
     {
         if (phased >= 1000)
         {
             phased = 831; // probes and the zero-bounce case stay on the phased kernel
         }
-        // SPK_RENDER_PHASED = warps*100 + min_blocks*10 + second_barrier selects a measured variant; 0 = render_kernel
+        // form = warps*100 + min_blocks*10 + second_barrier selects a measured variant; 1 = render_kernel
 #define SPK_PHASED_CASE(W, B, S2)                                                                                      \
     case W * 100 + B * 10 + S2:                                                                                        \
         if (!exact && !count)                                                                                          \
@@ -835,7 +947,7 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
             SPK_PHASED_CASE(16, 2, 1)
             SPK_PHASED_CASE(4, 6, 1)
         default:
-            set_error("spk_cuda_render: unknown SPK_RENDER_PHASED variant");
+            set_error("spk_cuda_render: unknown megakernel form (SPK_OPT_MEGAKERNEL_FORM)");
             return SPK_ERR_INVALID_ARGUMENT;
         }
 #undef SPK_PHASED_CASE
@@ -862,7 +974,7 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
                 render_kernel<true, false, true><<<grid, block, 0, ctx->stream>>>(scene, ctx->camera, a, ctx->d_gbuf, ctx->d_counters);
             SPK_CUDA_TRY(cudaGetLastError());
             ctx->stats.kernel_launches++;
-            int rc = launch_denoise_accumulate(ctx, 1u, a.accum_mode, ctx->accum_samples + s);
+            int rc = launch_denoise_accumulate(ctx, 1u, a.accum_mode, std::min(ctx->accum_samples + s, a.cumulated_cap));
             if (rc != SPK_OK)
             {
                 return rc;
@@ -983,11 +1095,11 @@ int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavef
     SPK_CUDA_TRY(cudaEventCreate(&e1));
     float ms[2] = {3.4e38f, 0.f};
     int rc = SPK_OK;
-    // candidates: the sorted megakernel with 16 warps x 2 CTAs/SM and with 8 warps x 4 CTAs/SM, then the wavefront tracer
+    // candidates: the persistent sorted megakernel with 16 warps x 2 CTAs/SM and with 8 warps x 4 CTAs/SM, then the wavefront tracer
     // (the phased kernel has not won on any scene since the sorted form keeps its path slots in shared memory; it stays
     // as the fallback for probes, zero-bounce and > 255-bounce launches). A later form replaces the incumbent only when
     // it is more than 3 % faster: short timings of near-equal forms are noise.
-    static const int kForms[3] = {1162, 1084, -1};
+    static const int kForms[3] = {2162, 2084, -1};
     int best_form = kForms[0];
     for (int which = 0; which < 3 && rc == SPK_OK; which++)
     {
@@ -1019,7 +1131,7 @@ int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavef
             ms[0] = best;
             best_form = kForms[which];
         }
-        if (getenv("SPK_VERBOSE"))
+        if (ctx->opt_verbose)
         {
             fprintf(stderr, "[spk_cuda] choose_tracer: form %d: %.3f ms per %u spp\n", kForms[which], best, p.sample_count);
         }

@@ -108,15 +108,6 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
 }
 } // namespace
 
-static int vote_setting()
-{
-    static int v = [] {
-        const char *e = getenv("SPK_VOTE");
-        return e ? atoi(e) : 6;
-    }();
-    return v;
-}
-
 template <bool CULL, bool COUNT, int VOTE>
 static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, float *hits)
 {
@@ -127,7 +118,8 @@ static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, fl
         SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, 0));
         SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
         blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
-        SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32, blocks_per_sm));
+        SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32, blocks_per_sm,
+                                                 ctx->opt_carveout));
     }
     uint64_t want = (n + kPersistWarps * 32 - 1) / (kPersistWarps * 32);
     uint64_t resident = uint64_t(blocks_per_sm) * sms; // one wave of persistent CTAs: a multiple of the SM count
@@ -174,7 +166,7 @@ int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *
         rc = launch_persistent<true, true, 8>(ctx, rays, n, hits);
     else
     {
-        switch (vote_setting())
+        switch (ctx->opt_vote)
         {
         case 4: rc = launch_persistent<true, false, 4>(ctx, rays, n, hits); break;
         case 8: rc = launch_persistent<true, false, 8>(ctx, rays, n, hits); break;

@@ -348,12 +348,6 @@ __global__ void __launch_bounds__(kShadeThreads)
 }
 } // namespace
 
-static uint32_t env_u32(const char *name, uint32_t dflt)
-{
-    const char *e = getenv(name);
-    return e && *e ? (uint32_t)strtoul(e, nullptr, 10) : dflt;
-}
-
 static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st)
 {
     // one allocation, carved into 256-byte aligned arrays
@@ -401,7 +395,8 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t 
         SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, extend, kExtendWarps * 32, 0));
         SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
         blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
-        SPK_CUDA_TRY(spk::prefer_small_carveout(extend, sizeof(uint32_t) * kExtendWarps * kLaneSmemWords * 32, blocks_per_sm));
+        SPK_CUDA_TRY(spk::prefer_small_carveout(extend, sizeof(uint32_t) * kExtendWarps * kLaneSmemWords * 32, blocks_per_sm,
+                                                 ctx->opt_carveout));
     }
     const unsigned long long total = (unsigned long long)a.width * a.height * sample_count;
     const uint32_t slots = st.slots;
@@ -416,7 +411,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t 
     // first look after the fewest iterations the job can take (one segment per path), then every few iterations
     unsigned long long least = (total + slots - 1) / slots + a.max_bounce;
     uint32_t chunk = uint32_t(least < 4096ull ? least : 4096ull);
-    const uint32_t chunk_next = env_u32("SPK_WF_CHUNK", 8);
+    const uint32_t chunk_next = ctx->opt_wf_chunk;
     uint32_t cur = 0;
     WfCtrl h{};
     for (;; chunk = chunk_next)
@@ -461,7 +456,7 @@ int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *p)
     a.max_bounce = p->max_bounce;
     a.output_limit = p->output_limit;
     const unsigned long long total = (unsigned long long)a.width * a.height * p->sample_count;
-    uint32_t slots = env_u32("SPK_WF_SLOTS", 1u << 24); // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
+    uint32_t slots = ctx->opt_wf_slots;
     if (slots > total)
     {
         slots = uint32_t(total);

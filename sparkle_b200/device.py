@@ -35,6 +35,10 @@ class CudaContext:
     def set_stream(self, cuda_stream):
         A.check(self.lib.spk_cuda_set_stream(self.handle, C.c_void_p(cuda_stream)))
 
+    def set_option(self, option, value):
+        """SpkOption tuning knobs (A.OPT_*): explicit, nothing is read from the environment"""
+        A.check(self.lib.spk_cuda_set_option(self.handle, option, int(value)))
+
     def upload_scene(self, desc):
         A.check(self.lib.spk_cuda_upload_scene(self.handle, C.byref(desc)))
 
@@ -48,8 +52,9 @@ class CudaContext:
         A.check(self.lib.spk_cuda_reset_accumulation(self.handle))
 
     def render(self, first_sample, sample_count, max_bounce=8, sample_stride=1, output_limit=6.0,
-               accum_mode=A.ACCUM_SUM, flags=0):
-        p = A.RenderParams(first_sample, sample_count, sample_stride, max_bounce, output_limit, accum_mode, flags, 0)
+               accum_mode=A.ACCUM_SUM, flags=0, cumulated_cap=0):
+        p = A.RenderParams(first_sample, sample_count, sample_stride, max_bounce, output_limit, accum_mode, flags,
+                           cumulated_cap)
         A.check(self.lib.spk_cuda_render(self.handle, C.byref(p)))
 
     def resolve(self, fmt=A.RESOLVE_LINEAR_F32, total_samples=0):

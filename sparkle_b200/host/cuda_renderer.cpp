@@ -705,6 +705,8 @@ void CudaRenderer::Render()
     p.accum_mode = SPK_ACCUM_RUNNING_AVERAGE; // the reference's temporal lerp (CPURenderer.cpp:530-544)
     // RenderConfig::spatial_denoise: g-buffer + neighbour fill per sample (CPURenderer.cpp:511-526)
     p.flags = render_config_.spatial_denoise ? SPK_FLAG_SPATIAL_DENOISE : 0u;
+    // past max_spp the camera's cumulated count stays at the cap: an exponential moving average (CameraRenderProxy.cpp:70-73)
+    p.cumulated_cap = render_config_.max_sample_per_pixel;
     rc = rc == SPK_OK ? spk_cuda_render(ctx_, &p) : rc;
     if (rc != SPK_OK)
     {

@@ -78,10 +78,10 @@ class Oracle:
         return hits, cnt
 
     def render(self, desc, cam, width, height, first_sample, sample_count, max_bounce=8, sample_stride=1,
-               accum_mode=A.ACCUM_SUM, accum=None, cumulated=0, threads=8, flags=0):
+               accum_mode=A.ACCUM_SUM, accum=None, cumulated=0, threads=8, flags=0, cumulated_cap=0):
         if accum is None:
             accum = np.zeros((height, width, 4), np.float32)
-        p = A.RenderParams(first_sample, sample_count, sample_stride, max_bounce, 6.0, accum_mode, flags, 0)
+        p = A.RenderParams(first_sample, sample_count, sample_stride, max_bounce, 6.0, accum_mode, flags, cumulated_cap)
         cum = C.c_uint32(cumulated)
         cnt = OrcCounters()
         rc = self.lib.orc_render(C.byref(desc), C.byref(cam), width, height, C.byref(p), accum.ctypes.data_as(A.fp),

@@ -83,6 +83,8 @@ def test_c2_full_resolution(oracle, monkeypatch):
     psnr = 10 * np.log10(max(ref[..., :3].max(), 1e-6) ** 2 / max(mse, 1e-30))
     print(f"C2 1920x1080 {spp} spp: mean rel err {rel.mean():.2e}, PSNR {psnr:.1f} dB, pixels > 1e-4: {(rel > 1e-4).mean():.2e}")
     assert rel.mean() <= 1e-3 and psnr > 40
+    import parity_report as PR
+    PR.report(f"c2_1920x1080_{spp}spp_vs_{oracle.kind}", whole, ref)
     ctx.close()
 
 

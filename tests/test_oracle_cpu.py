@@ -198,3 +198,39 @@ def test_spatial_denoise_port_equals_reference(tmp_path):
     assert np.array_equal(den, np.load(out))
     with pytest.raises(RuntimeError):
         O.Oracle("port").render(desc, cam, w, h, 0, 1, flags=A.FLAG_SPATIAL_DENOISE)  # sum mode: not the reference's pass
+
+
+@pytest.mark.skipif(not O.available("reference"), reason="oracle/_ref not built (needs /root/reference)")
+def test_running_average_cap_port_equals_reference(port):
+    """cumulated_cap (the camera's max_spp cap, CameraRenderProxy.cpp:70-73): port == reference bit for bit, and the
+    capped average differs from the running mean"""
+    ref = O.Oracle("reference")
+    sb, camkw = scenes.testscene()
+    desc = sb.finalize()
+    cam = orbit_camera(40, 30, **camkw)
+    a, _ = ref.render(desc, cam, 40, 30, 0, 6, accum_mode=A.ACCUM_RUNNING_AVERAGE, cumulated_cap=2, threads=2)
+    b, _ = port.render(desc, cam, 40, 30, 0, 6, accum_mode=A.ACCUM_RUNNING_AVERAGE, cumulated_cap=2, threads=2)
+    c, _ = port.render(desc, cam, 40, 30, 0, 6, accum_mode=A.ACCUM_RUNNING_AVERAGE, threads=2)
+    assert_same_bits(b, a, "capped running average")
+    assert np.abs(b - c).max() > 1e-3
+
+
+def test_device_libm_mode_of_the_port(port):
+    """orc_set_libm(1): sin/cos/pow in double, rounded once (what the CUDA path computes). Differs from glibc's float
+    routines by at most one ulp, on a small share of arguments; mode 0 restores the reference's bits."""
+    x = np.random.default_rng(5).uniform(0, 6.3, 20000).astype(np.float32)
+    base = np.array([port.kat_libm(0, v) for v in x[:2000]])
+    sb, camkw = scenes.testscene()
+    desc = sb.finalize()
+    cam = orbit_camera(48, 32, **camkw)
+    plain, _ = port.render(desc, cam, 48, 32, 0, 4, threads=2)
+    try:
+        port.set_libm(True)
+        dev, _ = port.render(desc, cam, 48, 32, 0, 4, threads=2)
+    finally:
+        port.set_libm(False)
+    again, _ = port.render(desc, cam, 48, 32, 0, 4, threads=2)
+    assert_same_bits(again, plain, "mode 0 restored")
+    rel = np.abs(dev[..., :3] - plain[..., :3]).sum(-1) / np.maximum(plain[..., :3].sum(-1), 1e-3)
+    assert rel.mean() < 1e-3 and (dev != plain).any(), rel.mean()
+    assert np.array_equal(base, np.array([port.kat_libm(0, v) for v in x[:2000]]))

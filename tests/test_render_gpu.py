@@ -5,6 +5,7 @@ cos and pow in double and rounds once; glibc's float versions differ by one ulp 
 import numpy as np
 import pytest
 
+import parity_report as PR
 from sparkle_b200 import _abi as A
 from sparkle_b200 import scenes
 from sparkle_b200.device import CudaContext
@@ -15,13 +16,12 @@ pytestmark = pytest.mark.gpu
 MEAN_REL_TOL = 1e-3
 
 
-def image_metrics(gpu, ref):
-    g, r = gpu[..., :3].astype(np.float64), ref[..., :3].astype(np.float64)
-    rel = np.abs(g - r).sum(-1) / np.maximum(r.sum(-1), 1e-3)
-    mse = np.mean((g - r) ** 2)
-    peak = max(r.max(), 1e-6)
-    psnr = float("inf") if mse == 0 else 10 * np.log10(peak * peak / mse)
-    return dict(mean_rel=float(rel.mean()), max_rel=float(rel.max()), frac_gt_1e4=float((rel > 1e-4).mean()), psnr=psnr)
+def image_metrics(gpu, ref, name=None):
+    """aggregate metrics + worst 8x8 tile; with a name also the signed-difference image and a report line
+    (tests/parity_report.py, SURVEY.md section 4: never aggregate-only)"""
+    if name:
+        return PR.report(name, gpu, ref)
+    return PR.metrics(gpu, ref)[0]
 
 
 def build(name, w, h):
@@ -67,8 +67,7 @@ def test_image_tolerance(name, bounce, spp, oracle):
     ctx.set_camera(cam)
     ctx.render(first_sample=0, sample_count=spp, max_bounce=bounce)
     gpu = ctx.resolve(A.RESOLVE_LINEAR_F32)
-    m = image_metrics(gpu, ref)
-    print(name, spp, m)
+    m = image_metrics(gpu, ref, f"image_tolerance_{name}_{spp}spp")
     assert m["mean_rel"] <= MEAN_REL_TOL, m
     assert m["psnr"] > 40.0, m
     # exact (never-culled) traversal gives the same image as the culled one
@@ -127,7 +126,7 @@ def test_running_average_and_resolve_formats(oracle):
 
 
 @pytest.mark.parametrize("name,bounce,spp", [("testscene", 8, 8), ("city", 8, 4), ("room", 32, 4)])
-def test_wavefront_equals_megakernel(name, bounce, spp, oracle, monkeypatch):
+def test_wavefront_equals_megakernel(name, bounce, spp, oracle):
     """SPK_FLAG_WAVEFRONT: the same samples through the queue tracer; only the order of the per-pixel sum differs"""
     w, h = 128, 72
     sb, desc, cam = build(name, w, h)
@@ -137,8 +136,8 @@ def test_wavefront_equals_megakernel(name, bounce, spp, oracle, monkeypatch):
     ctx.render(first_sample=2, sample_count=spp, max_bounce=bounce)
     mega = ctx.resolve(A.RESOLVE_LINEAR_F32)
     st_m = ctx.stats()
-    for slots in ("1024", "1048576"):  # pool smaller than one sample of the image / larger than the whole job
-        monkeypatch.setenv("SPK_WF_SLOTS", slots)
+    for slots in (1024, 1048576):  # pool smaller than one sample of the image / larger than the whole job
+        ctx.set_option(A.OPT_WAVEFRONT_SLOTS, slots)
         ctx.reset_accumulation()
         ctx.reset_stats()
         ctx.render(first_sample=2, sample_count=spp, max_bounce=bounce, flags=A.FLAG_WAVEFRONT)
@@ -184,6 +183,6 @@ def test_spatial_denoise(oracle):
     assert m["frac_gt_1e4"] < 0.01, m
     # the filled pixels carry the neighbour's colour exactly as in the reference
     rel = np.abs(gpu[..., :3] - ref[..., :3]).sum(-1) / np.maximum(ref[..., :3].sum(-1), 1e-3)
-    assert (rel[changed] < 1e-4).mean() > 0.9, rel[changed]
+    assert (rel[changed] < 1e-4).mean() > 0.97, rel[changed]
     assert np.array_equal(gpu[..., 3][changed], ref[..., 3][changed])
     ctx.close()

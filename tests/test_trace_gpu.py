@@ -93,3 +93,39 @@ def test_errors():
         ctx.upload_scene(d)
     assert e.value.code == A.ERR_INVALID_ARGUMENT
     ctx.close()
+
+
+def test_update_instances_validation_and_extent(oracle):
+    """spk_cuda_update_instances: a stale material index is rejected (it would index the device material table out of
+    bounds), and instances moved far outside the uploaded world bounds still give culled == exact == oracle: the
+    t-culling slack is re-derived from the rebuilt TLAS root."""
+    sb, _ = scenes.city(num_meshes=3, tris_per_mesh=400, num_instances=12)
+    desc = sb.finalize()
+    ctx = CudaContext(64, 64)
+    ctx.upload_scene(desc)
+    bad = sb.primitive_array()
+    bad[2].material = len(sb.materials) + 5
+    with pytest.raises(A.SpkError) as e:
+        ctx.update_instances(bad, len(sb.prims), sb.tlas.desc())
+    assert e.value.code == A.ERR_INVALID_ARGUMENT and "material" in str(e.value)
+    # move every instance 400 units out (the upload's extent was ~30): rebuild the TLAS host-side, update, trace
+    from sparkle_b200.geometry import trs
+    for p in sb.prims[1:]:
+        t, eul, scl = p["trs"]
+        t2 = (t[0] + 400.0, t[1] - 250.0, t[2])
+        fwd, inv = trs(t2, eul, scl)
+        lo, hi = sb.meshes[p["mesh"]].bounds()
+        corners = np.array([[x, y, z] for x in (lo[0], hi[0]) for y in (lo[1], hi[1]) for z in (lo[2], hi[2])], np.float32)
+        wc = corners @ fwd[:, :3].T + fwd[:, 3]
+        p.update(fwd=fwd, inv=inv, lo=wc.min(axis=0), hi=wc.max(axis=0), trs=(t2, eul, scl))
+    moved = sb.finalize()  # same meshes, new transforms and TLAS
+    ctx.update_instances(sb.primitive_array(), len(sb.prims), sb.tlas.desc())
+    rays = geometry.random_rays(50_000, seed=9, extent=20.0)
+    rays[:, 0] += 400.0
+    rays[:, 1] -= 250.0
+    rays[:, 2] = np.abs(rays[:, 2]) * 0.3 + 0.1
+    ref, _ = oracle.trace_closest(moved, rays)
+    assert (ref["prim"] != A.INVALID_ID).mean() > 0.05
+    assert_hits_equal(ctx.trace_closest(rays, A.FLAG_EXACT_TRAVERSAL), ref, "moved, exact")
+    assert_hits_equal(ctx.trace_closest(rays), ref, "moved, culled")
+    ctx.close()
