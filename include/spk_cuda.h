@@ -12,9 +12,10 @@
  *     throws across the boundary.
  *   - the context owns all device memory; the caller owns all host memory. Host pointers in
  *     SpkSceneDesc are borrowed for the duration of the call only.
- *   - one context == one CUDA device == one stream. Multi-GPU = one process (context) per GPU, spp
- *     interleaved by (first_sample, sample_stride), accumulators summed by the caller with one NCCL
- *     reduce on the pointer spk_cuda_accum_device_ptr() returns.
+ *   - one context == one CUDA device == one stream. Multi-GPU = one context per GPU (in one process or one
+ *     process each), spp interleaved by (first_sample, sample_stride), accumulators combined and tone-mapped by
+ *     spk_cuda_group_resolve over NVLink peer memory; spk_cuda_accum_device_ptr() stays for callers
+ *     that bring their own collective (one NCCL reduce).
  *   - there is NO CPU fallback: without a CUDA device spk_cuda_create fails with SPK_ERR_NO_DEVICE.
  */
 #ifndef SPK_CUDA_H_
@@ -243,6 +244,11 @@ uint32_t spk_cuda_abi_version(void);
 /* Renderer::CreateRenderer + CudaRenderer::InitRenderResources (Renderer.cpp:17-53). */
 int spk_cuda_create(const SpkCreateInfo *info, SpkContext **out);
 int spk_cuda_destroy(SpkContext *ctx);
+/* Page-locked host memory for frame buffers and ray batches: spk_cuda_resolve / spk_cuda_trace_closest copy to and from
+ * such buffers with one DMA at PCIe speed; any other host pointer works too and is staged through a pinned bounce
+ * buffer inside the call. (The reference's readback buffer is an RHI staging buffer, Renderer.cpp:108-180.) */
+int spk_cuda_host_alloc(void **out, size_t bytes);
+int spk_cuda_host_free(void *p);
 /* Use an externally owned cudaStream_t (e.g. torch's current stream) instead of the context's own. */
 int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream);
 
@@ -280,12 +286,38 @@ int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_ray
 int spk_cuda_trace_closest_device(SpkContext *ctx, const void *d_rays, uint64_t num_rays, void *d_hits,
                                   uint32_t flags);
 
+/* ---- multi-GPU behind the boundary (north_star (d)) ---------------------------------------------------
+ * The scene is replicated, rank g of G renders samples {g, g+G, ...} (first_sample = g, sample_stride = G) into its own
+ * accumulator, and ONE kernel per GPU combines them: each GPU sums its H/G rows of all G accumulators over NVLink peer
+ * memory, tone-maps them (ToneMappingPass, CPURenderer.cpp:554-576) and stores the packed pixels into the root's output
+ * buffer; the root copies the frame to `host_out`. Reduce-scatter + resolve + gather in one pass (csrc/spk_group.cu).
+ *   local group  all contexts live in this process (CudaRenderer with the `gpus` cvar): one call drives every GPU.
+ *   IPC group    one process per GPU (torchrun): every rank exports a handle, the host exchanges them (any transport),
+ *                every rank creates its group object and makes the SAME resolve calls; rank 0 is the root and the only
+ *                one whose host_out is written (others pass NULL). One rank per GPU. A NULL host_out on the root leaves
+ *                the frame in the root's device buffer and does not block. */
+#define SPK_PEER_HANDLE_BYTES 192
+typedef struct SpkPeerHandle {
+    uint8_t bytes[SPK_PEER_HANDLE_BYTES];
+} SpkPeerHandle;
+typedef struct SpkGroup SpkGroup;
+int spk_cuda_group_export(SpkContext *ctx, SpkPeerHandle *out);
+int spk_cuda_group_create(SpkContext *ctx, uint32_t rank, uint32_t world, const SpkPeerHandle *handles, SpkGroup **out);
+int spk_cuda_group_create_local(SpkContext *const *ctxs, uint32_t n, SpkGroup **out);
+/* `total_samples`: samples summed over all ranks (SPK_ACCUM_SUM divides by it). */
+int spk_cuda_group_resolve(SpkGroup *group, uint32_t format, uint32_t total_samples, void *host_out, size_t host_bytes);
+/* IPC groups: by default ranks > 0 return from spk_cuda_group_resolve when their kernel has finished (so a rank that
+ * never joined is reported to everyone); enabled = 1 makes them return at once, like the root with host_out == NULL. */
+int spk_cuda_group_set_async(SpkGroup *group, uint32_t enabled);
+int spk_cuda_group_destroy(SpkGroup *group);
+
 /* Tuning knobs, explicit (nothing in the library reads the environment). Defaults are the measured choices. */
 typedef enum SpkOption {
-    SPK_OPT_MEGAKERNEL_FORM = 0, /* 0 = measured choice (spk_cuda_choose_tracer; 2162 until measured). Forms: 2162 / 2084
-                                    persistent pixel-pulling sorted megakernel, 16 warps x 2 / 8 warps x 4 CTAs per SM;
-                                    1162 / 1084 / 1083 the same with pixels owned by a CTA (round-1 form); 831 / 830 /
-                                    1621 / 461 phased kernel; 1 = plain per-pixel loop */
+    SPK_OPT_MEGAKERNEL_FORM = 0, /* 0 = measured choice (spk_cuda_choose_tracer; 1162 until measured). Forms: 1162 / 1084 /
+                                    1083 sorted megakernel, 16 warps x 2 / 8 x 4 / 8 x 3 CTAs per SM, pixels owned by a
+                                    CTA; 3162 / 3084 the same with the sort kept in pixel order inside a class; 2162 /
+                                    2084 persistent pixel-pulling grid; 831 / 830 / 1621 / 461 phased kernel; 1 = plain
+                                    per-pixel loop */
     SPK_OPT_WAVEFRONT_SLOTS = 1, /* path slots of the wavefront tracer (default 2^24; 100 bytes each) */
     SPK_OPT_WAVEFRONT_CHUNK = 2, /* wavefront iterations queued per host read of the control block (default 8) */
     SPK_OPT_TRACE_VOTE = 3,      /* ray-batch kernel: lanes waiting in a leaf state that switch the warp to it (4, 6, 8, 12, 16; default 6) */

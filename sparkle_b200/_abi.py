@@ -93,6 +93,13 @@ class CreateInfo(C.Structure):
 
 
 CtxP = C.c_void_p
+GroupP = C.c_void_p
+PEER_HANDLE_BYTES = 192
+
+
+class PeerHandle(C.Structure):
+    _fields_ = [("bytes", C.c_uint8 * PEER_HANDLE_BYTES)]
+
 
 # every symbol include/spk_cuda.h declares: name -> (restype, argtypes)
 CUDA_SYMBOLS = {
@@ -100,6 +107,8 @@ CUDA_SYMBOLS = {
     "spk_cuda_abi_version": (u32, []),
     "spk_cuda_create": (C.c_int, [C.POINTER(CreateInfo), C.POINTER(CtxP)]),
     "spk_cuda_destroy": (C.c_int, [CtxP]),
+    "spk_cuda_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "spk_cuda_host_free": (C.c_int, [C.c_void_p]),
     "spk_cuda_set_stream": (C.c_int, [CtxP, C.c_void_p]),
     "spk_cuda_set_option": (C.c_int, [CtxP, u32, C.c_int64]),
     "spk_cuda_upload_scene": (C.c_int, [CtxP, C.POINTER(SceneDesc)]),
@@ -114,6 +123,12 @@ CUDA_SYMBOLS = {
     "spk_cuda_accum_sample_count": (C.c_int, [CtxP, u32p]),
     "spk_cuda_trace_closest": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
     "spk_cuda_trace_closest_device": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
+    "spk_cuda_group_export": (C.c_int, [CtxP, C.POINTER(PeerHandle)]),
+    "spk_cuda_group_create": (C.c_int, [CtxP, u32, u32, C.POINTER(PeerHandle), C.POINTER(GroupP)]),
+    "spk_cuda_group_create_local": (C.c_int, [C.POINTER(CtxP), u32, C.POINTER(GroupP)]),
+    "spk_cuda_group_resolve": (C.c_int, [GroupP, u32, u32, C.c_void_p, C.c_size_t]),
+    "spk_cuda_group_set_async": (C.c_int, [GroupP, u32]),
+    "spk_cuda_group_destroy": (C.c_int, [GroupP]),
     "spk_cuda_get_stats": (C.c_int, [CtxP, C.POINTER(Stats)]),
     "spk_cuda_reset_stats": (C.c_int, [CtxP]),
     "spk_cuda_synchronize": (C.c_int, [CtxP]),

@@ -29,6 +29,17 @@ int cuda_fail(cudaError_t e, const char *what)
     return e == cudaErrorMemoryAllocation ? SPK_ERR_OUT_OF_MEMORY : SPK_ERR_CUDA;
 }
 
+int ensure_accum_cleared(SpkContext *ctx)
+{
+    if (ctx->accum_clear_pending)
+    {
+        SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+        SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_accum, 0, size_t(ctx->width) * ctx->height * sizeof(float4), ctx->stream));
+        ctx->accum_clear_pending = false;
+    }
+    return SPK_OK;
+}
+
 namespace
 {
 int invalid(const char *msg)
@@ -97,11 +108,15 @@ int validate_bvh(const SpkBvhDesc &d, uint32_t expected_prims, const char *what)
     // iterative depth check
     std::vector<std::pair<uint32_t, uint32_t>> todo;
     todo.emplace_back(0u, 0u);
-    uint64_t leaf_prims = 0;
+    uint64_t leaf_prims = 0, visited = 0;
     while (!todo.empty())
     {
         auto [id, depth] = todo.back();
         todo.pop_back();
+        if (++visited > d.num_nodes)
+        {
+            return invalid(what); // children shared between parents (a DAG): a tree visits every node once
+        }
         HostNode n = read_node(d, id);
         uint32_t count = n.index & 15u, first = n.index >> 4;
         if (count == 0)
@@ -161,22 +176,43 @@ uint32_t root_word(const SpkBvhDesc &d, uint32_t pair_base, uint32_t leaf_base)
     return count == 0 ? ((pair_base + (first - 1) / 2) << 4) : (((leaf_base + first) << 4) | count);
 }
 
-template <typename T> int upload(SpkContext *ctx, const T *src, size_t count, T **out, bool keep = true)
+// ---- scene arena ----
+// Every table of a scene lives in ONE device allocation (ctx->d_arena) filled from ONE pinned staging buffer with ONE
+// cudaMemcpyAsync and one synchronize. Both are kept across uploads and only grow: re-uploading a scene of the same
+// size (the per-frame e2e path, CudaRenderer::Update after a topology change) costs no cudaMalloc / cudaFree at all.
+// Round 1 did a cudaMalloc + pageable copy + stream synchronize per table (about 70 per scene) and freed them all on
+// the next upload: a fixed 1-3 ms per end-to-end step that did not shrink with the number of GPUs.
+struct ArenaPlan
 {
-    *out = nullptr;
-    if (count == 0)
+    size_t used = 0;
+    size_t add(size_t bytes)
     {
-        return SPK_OK;
+        const size_t at = used;
+        used += (bytes + 255u) & ~size_t(255u); // 256-byte slots: every table is aligned for 128/256-bit loads
+        return at;
     }
-    void *p = nullptr;
-    SPK_CUDA_TRY(cudaMalloc(&p, count * sizeof(T)));
-    if (keep)
+};
+
+int arena_reserve(SpkContext *ctx, size_t bytes)
+{
+    if (ctx->arena_capacity < bytes)
     {
-        ctx->scene_allocs.push_back(p);
+        cudaFree(ctx->d_arena);
+        ctx->d_arena = nullptr;
+        ctx->arena_capacity = 0;
+        const size_t want = bytes + bytes / 8; // head-room for a slightly larger re-upload
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_arena, want));
+        ctx->arena_capacity = want;
     }
-    SPK_CUDA_TRY(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
-    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream)); // host pointers are borrowed for this call only
-    *out = static_cast<T *>(p);
+    if (ctx->stage_capacity < bytes)
+    {
+        cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr;
+        ctx->stage_capacity = 0;
+        const size_t want = bytes + bytes / 8;
+        SPK_CUDA_TRY(cudaHostAlloc(&ctx->h_stage, want, cudaHostAllocDefault));
+        ctx->stage_capacity = want;
+    }
     return SPK_OK;
 }
 
@@ -196,35 +232,9 @@ size_t texel_bytes(uint32_t format)
     }
 }
 
-int upload_texture(SpkContext *ctx, const SpkTextureDesc &t, DTexture &out)
-{
-    size_t tb = texel_bytes(t.format);
-    if (!t.pixels || t.width == 0 || t.height == 0 || tb == 0)
-    {
-        return invalid("texture descriptor");
-    }
-    uint8_t *p = nullptr;
-    int rc = upload(ctx, static_cast<const uint8_t *>(t.pixels), size_t(t.width) * t.height * tb, &p);
-    if (rc != SPK_OK)
-    {
-        return rc;
-    }
-    out.pixels = p;
-    out.width = t.width;
-    out.height = t.height;
-    out.format = t.format;
-    out.pad = 0;
-    return SPK_OK;
-}
-
 void free_scene(SpkContext *ctx)
 {
-    for (void *p : ctx->scene_allocs)
-    {
-        cudaFree(p);
-    }
-    ctx->scene_allocs.clear();
-    ctx->has_scene = false;
+    ctx->has_scene = false; // the arena and its staging buffer stay for the next upload (spk_cuda_destroy frees them)
     ctx->scene = DScene{};
     ctx->mesh_root_word.clear();
     ctx->d_pairs = nullptr;
@@ -288,14 +298,26 @@ int spk_cuda_create(const SpkCreateInfo *info, SpkContext **out)
     ctx->device = info->device;
     ctx->width = info->width;
     ctx->height = info->height;
-    SPK_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    SPK_CUDA_TRY(cudaEventCreate(&ctx->ev0));
-    SPK_CUDA_TRY(cudaEventCreate(&ctx->ev1));
-    SPK_CUDA_TRY(cudaMalloc(&ctx->d_accum, size_t(info->width) * info->height * sizeof(float4)));
-    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_accum, 0, size_t(info->width) * info->height * sizeof(float4), ctx->stream));
-    SPK_CUDA_TRY(cudaMalloc(&ctx->d_counters, 8 * sizeof(unsigned long long)));
-    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
-    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    // any failure below releases what was created so far (spk_cuda_destroy accepts a half-built context)
+    auto init = [&]() -> int {
+        SPK_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        SPK_CUDA_TRY(cudaEventCreate(&ctx->ev0));
+        SPK_CUDA_TRY(cudaEventCreate(&ctx->ev1));
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_accum, size_t(info->width) * info->height * sizeof(float4)));
+        SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_accum, 0, size_t(info->width) * info->height * sizeof(float4), ctx->stream));
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_counters, 8 * sizeof(unsigned long long)));
+        SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+        SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        return SPK_OK;
+    };
+    const int rc = init();
+    if (rc != SPK_OK)
+    {
+        const std::string why = g_last_error;
+        spk_cuda_destroy(ctx);
+        set_error(why);
+        return rc;
+    }
     *out = ctx;
     return SPK_OK;
 }
@@ -307,18 +329,38 @@ int spk_cuda_destroy(SpkContext *ctx)
         return SPK_OK;
     }
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    if (ctx->stream)
+    {
+        cudaStreamSynchronize(ctx->stream);
+    }
     free_scene(ctx);
+    cudaFree(ctx->d_arena);
+    cudaFreeHost(ctx->h_stage);
+    cudaFreeHost(ctx->h_resolve);
+    for (cudaEvent_t e : ctx->resolve_ev)
+    {
+        if (e)
+        {
+            cudaEventDestroy(e);
+        }
+    }
     cudaFree(ctx->d_accum);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_rays);
     cudaFree(ctx->d_hits);
     cudaFree(ctx->d_resolve);
     cudaFree(ctx->wf_block);
+    cudaFree(ctx->d_group_block);
     cudaFree(ctx->d_gbuf);
-    cudaEventDestroy(ctx->ev0);
-    cudaEventDestroy(ctx->ev1);
-    if (ctx->own_stream)
+    if (ctx->ev0)
+    {
+        cudaEventDestroy(ctx->ev0);
+    }
+    if (ctx->ev1)
+    {
+        cudaEventDestroy(ctx->ev1);
+    }
+    if (ctx->own_stream && ctx->stream)
     {
         cudaStreamDestroy(ctx->stream);
     }
@@ -375,6 +417,26 @@ int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value)
     default:
         return invalid("spk_cuda_set_option: unknown option");
     }
+}
+
+int spk_cuda_host_alloc(void **out, size_t bytes)
+{
+    if (!out || bytes == 0)
+    {
+        return invalid("spk_cuda_host_alloc: null argument or zero size");
+    }
+    *out = nullptr;
+    SPK_CUDA_TRY(cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+    return SPK_OK;
+}
+
+int spk_cuda_host_free(void *p)
+{
+    if (p)
+    {
+        SPK_CUDA_TRY(cudaFreeHost(p));
+    }
+    return SPK_OK;
 }
 
 int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream)
@@ -486,32 +548,92 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         return invalid("spk_cuda_upload_scene: scene exceeds 2^28 pairs or triangles");
     }
 
-    // ---- flatten BLAS pairs + triangles (leaf order) ----
-    // uninitialised on purpose: every word is written below, and zero-filling 80 MB first costs tens of ms of page faults
-    // on one thread (the parallel writers below take the faults instead). One spare pair so an all-leaf scene still has
-    // a valid (never dereferenced) pointer.
-    const size_t pair_floats = size_t(total_pairs) * 16 + 16, tri_floats = size_t(total_tris) * 12;
-    std::unique_ptr<float[]> pairs_buf(new (std::nothrow) float[pair_floats]);
-    std::unique_ptr<float[]> tris_buf(new (std::nothrow) float[tri_floats ? tri_floats : 1]);
-    if (!pairs_buf || !tris_buf)
+    // ---- texture descriptors are checked before anything is laid out ----
+    auto texture_ok = [](const SpkTextureDesc &t) { return t.pixels && t.width && t.height && texel_bytes(t.format); };
+    for (uint32_t t = 0; t < s->num_textures; t++)
     {
-        return SPK_ERR_OUT_OF_MEMORY;
+        if (!texture_ok(s->textures[t]))
+        {
+            return invalid("texture descriptor");
+        }
     }
-    memset(pairs_buf.get() + size_t(total_pairs) * 16, 0, 64);
-    struct
+    const bool sky_map = s->sky.has_sky && s->sky.has_map;
+    for (int f = 0; sky_map && f < 6; f++)
     {
-        float *p;
-        float *data() const { return p; }
-    } pairs{pairs_buf.get()}, tris{tris_buf.get()};
-    std::vector<DMesh> dmeshes(s->num_meshes);
+        if (!texture_ok(s->sky.faces[f]))
+        {
+            return invalid("texture descriptor");
+        }
+    }
+
+    // ---- lay the arena out (offsets only) ----
+    ArenaPlan plan;
+    // one spare pair so an all-leaf scene still has a valid (never dereferenced) pointer
+    const size_t off_pairs = plan.add(size_t(total_pairs) * 64 + 64);
+    const size_t off_tris = plan.add(size_t(total_tris) * 48);
+    const size_t off_inst = plan.add(size_t(s->num_primitives) * sizeof(DInstance));
+    const size_t off_meshes = plan.add(size_t(s->num_meshes) * sizeof(DMesh));
+    const size_t off_mats = plan.add(size_t(s->num_materials) * sizeof(DMaterial));
+    const size_t off_tex = plan.add(size_t(s->num_textures) * sizeof(DTexture));
+    struct MeshOffsets
+    {
+        size_t normals, tangents, indices, uvs;
+    };
+    std::vector<MeshOffsets> mesh_off(s->num_meshes);
+    for (uint32_t m = 0; m < s->num_meshes; m++)
+    {
+        const SpkMeshDesc &md = s->meshes[m];
+        mesh_off[m].normals = plan.add(size_t(md.num_vertices) * 12);
+        mesh_off[m].tangents = plan.add(size_t(md.num_vertices) * 16);
+        mesh_off[m].indices = plan.add(size_t(md.num_faces) * 12);
+        mesh_off[m].uvs = md.uvs ? plan.add(size_t(md.num_vertices) * 8) : 0;
+    }
+    auto texture_bytes = [](const SpkTextureDesc &t) { return size_t(t.width) * t.height * texel_bytes(t.format); };
+    std::vector<size_t> tex_off(s->num_textures);
+    for (uint32_t t = 0; t < s->num_textures; t++)
+    {
+        tex_off[t] = plan.add(texture_bytes(s->textures[t]));
+    }
+    size_t sky_off[6] = {0, 0, 0, 0, 0, 0};
+    for (int f = 0; sky_map && f < 6; f++)
+    {
+        sky_off[f] = plan.add(texture_bytes(s->sky.faces[f]));
+    }
+    if ((rc = arena_reserve(ctx, plan.used)) != SPK_OK)
+    {
+        return rc;
+    }
+    uint8_t *const stage = static_cast<uint8_t *>(ctx->h_stage);
+    uint8_t *const dev = static_cast<uint8_t *>(ctx->d_arena);
+
+    // ---- flatten BLAS pairs + triangles (leaf order) straight into the pinned staging buffer ----
+    // (every word of both tables is written below; nothing is zero-filled first)
+    float *const pairs = reinterpret_cast<float *>(stage + off_pairs);
+    float *const tris = reinterpret_cast<float *>(stage + off_tris);
+    memset(pairs + size_t(total_pairs) * 16, 0, 64);
     ctx->mesh_root_word.assign(s->num_meshes, 0);
     uint32_t pair_base = 0, tri_base = 0;
-    // work items: one flatten_pairs per mesh, and the triangle records in chunks of 64 Ki faces
+    // work items: one flatten_pairs per mesh, the triangle records in chunks of 64 Ki faces, and plain copies of the
+    // attribute / texture arrays in chunks of 4 MiB
     struct Item
     {
         uint32_t mesh, pair_base, tri_base, begin, end; // begin == end: the pair item
+        const void *src = nullptr;                     // != nullptr: a plain copy of `bytes` to stage + dst
+        size_t dst = 0, bytes = 0;
     };
     std::vector<Item> items;
+    auto add_copy = [&](const void *src, size_t dst, size_t bytes) {
+        const size_t chunk = size_t(4) << 20;
+        for (size_t at = 0; at < bytes; at += chunk)
+        {
+            Item it{};
+            it.src = static_cast<const uint8_t *>(src) + at;
+            it.dst = dst + at;
+            it.bytes = std::min(chunk, bytes - at);
+            items.push_back(it);
+        }
+    };
+    DMesh *const dmeshes = reinterpret_cast<DMesh *>(stage + off_meshes);
     for (uint32_t m = 0; m < s->num_meshes; m++)
     {
         const SpkMeshDesc &md = s->meshes[m];
@@ -522,13 +644,58 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         }
         pair_base += (md.blas.num_nodes - 1) / 2;
         tri_base += md.num_faces;
+        add_copy(md.normals, mesh_off[m].normals, size_t(md.num_vertices) * 12);
+        add_copy(md.tangents, mesh_off[m].tangents, size_t(md.num_vertices) * 16);
+        add_copy(md.indices, mesh_off[m].indices, size_t(md.num_faces) * 12);
+        if (md.uvs)
+        {
+            add_copy(md.uvs, mesh_off[m].uvs, size_t(md.num_vertices) * 8);
+        }
+        dmeshes[m].normals = reinterpret_cast<const float *>(dev + mesh_off[m].normals);
+        dmeshes[m].tangents = reinterpret_cast<const float *>(dev + mesh_off[m].tangents);
+        dmeshes[m].indices = reinterpret_cast<const uint32_t *>(dev + mesh_off[m].indices);
+        dmeshes[m].uvs = md.uvs ? reinterpret_cast<const float *>(dev + mesh_off[m].uvs) : nullptr;
+    }
+    DTexture *const dtex = reinterpret_cast<DTexture *>(stage + off_tex);
+    auto device_texture = [&](const SpkTextureDesc &t, size_t off) {
+        DTexture d;
+        d.pixels = dev + off;
+        d.width = t.width;
+        d.height = t.height;
+        d.format = t.format;
+        d.pad = 0;
+        return d;
+    };
+    for (uint32_t t = 0; t < s->num_textures; t++)
+    {
+        add_copy(s->textures[t].pixels, tex_off[t], texture_bytes(s->textures[t]));
+        dtex[t] = device_texture(s->textures[t], tex_off[t]);
+    }
+    DSky sky{};
+    sky.has_sky = s->sky.has_sky;
+    sky.has_map = sky_map ? 1u : 0u;
+    memcpy(sky.color, s->sky.color, 12);
+    for (int f = 0; sky_map && f < 6; f++)
+    {
+        add_copy(s->sky.faces[f].pixels, sky_off[f], texture_bytes(s->sky.faces[f]));
+        sky.faces[f] = device_texture(s->sky.faces[f], sky_off[f]);
+    }
+    static_assert(sizeof(SpkMaterialDesc) == sizeof(DMaterial), "material ABI == device record");
+    if (s->num_materials)
+    {
+        memcpy(stage + off_mats, s->materials, size_t(s->num_materials) * sizeof(DMaterial));
     }
     parallel_for(items.size(), [&](size_t w) {
         const Item &it = items[w];
+        if (it.src)
+        {
+            memcpy(stage + it.dst, it.src, it.bytes);
+            return;
+        }
         const SpkMeshDesc &md = s->meshes[it.mesh];
         if (it.begin == it.end)
         {
-            flatten_pairs(md.blas, it.pair_base, it.tri_base, pairs.data() + size_t(it.pair_base) * 16);
+            flatten_pairs(md.blas, it.pair_base, it.tri_base, pairs + size_t(it.pair_base) * 16);
             ctx->mesh_root_word[it.mesh] = root_word(md.blas, it.pair_base, it.tri_base);
             return;
         }
@@ -538,7 +705,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
             const float *v0 = md.vertices + size_t(md.indices[size_t(face) * 3 + 0]) * 3;
             const float *v1 = md.vertices + size_t(md.indices[size_t(face) * 3 + 1]) * 3;
             const float *v2 = md.vertices + size_t(md.indices[size_t(face) * 3 + 2]) * 3;
-            float *o = tris.data() + size_t(it.tri_base + k) * 12;
+            float *o = tris + size_t(it.tri_base + k) * 12;
             // Triangle::Set (MeshRenderProxy.cpp:80-86): p0 = v0, e1 = v1 - v0, e2 = v2 - v0
             for (int a = 0; a < 3; a++)
             {
@@ -551,28 +718,6 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
             o[11] = 0.f;
         }
     });
-    pair_base = 0;
-    tri_base = 0;
-    for (uint32_t m = 0; m < s->num_meshes; m++)
-    {
-        const SpkMeshDesc &md = s->meshes[m];
-        float *dn = nullptr, *dt = nullptr, *du = nullptr;
-        uint32_t *di = nullptr;
-        if ((rc = upload(ctx, md.normals, size_t(md.num_vertices) * 3, &dn)) != SPK_OK ||
-            (rc = upload(ctx, md.tangents, size_t(md.num_vertices) * 4, &dt)) != SPK_OK ||
-            (rc = upload(ctx, md.indices, size_t(md.num_faces) * 3, &di)) != SPK_OK ||
-            (md.uvs && (rc = upload(ctx, md.uvs, size_t(md.num_vertices) * 2, &du)) != SPK_OK))
-        {
-            free_scene(ctx);
-            return rc;
-        }
-        dmeshes[m].normals = dn;
-        dmeshes[m].tangents = dt;
-        dmeshes[m].uvs = du;
-        dmeshes[m].indices = di;
-        pair_base += (md.blas.num_nodes - 1) / 2;
-        tri_base += md.num_faces;
-    }
     ctx->num_blas_pairs = pair_base;
     ctx->tlas_pair_base = pair_base;
 
@@ -585,10 +730,11 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         ctx->material_class[m] = (md.type == SPK_MAT_DIELECTRIC ? 2u : 0u) + (textured ? 4u : 0u) + (emissive ? 8u : 0u);
     }
     // ---- TLAS pairs + instances in TLAS leaf order (SceneRenderProxy.cpp:59-68) ----
-    std::vector<DInstance> instances(s->num_primitives);
+    DInstance *const instances = reinterpret_cast<DInstance *>(stage + off_inst);
+    ctx->scene = DScene{};
     if (s->num_primitives)
     {
-        flatten_pairs(s->tlas, pair_base, 0, pairs.data() + size_t(pair_base) * 16);
+        flatten_pairs(s->tlas, pair_base, 0, pairs + size_t(pair_base) * 16);
         ctx->scene.tlas_root = root_word(s->tlas, pair_base, 0);
         for (uint32_t k = 0; k < s->num_primitives; k++)
         {
@@ -599,61 +745,18 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     ctx->pair_capacity = uint32_t(total_pairs);
     ctx->instance_capacity = s->num_primitives;
 
-    float4 *d_pairs = nullptr, *d_tris = nullptr;
-    DInstance *d_inst = nullptr;
-    DMesh *d_meshes = nullptr;
-    if ((rc = upload(ctx, reinterpret_cast<const float4 *>(pairs.data()), pair_floats / 4, &d_pairs)) != SPK_OK ||
-        (rc = upload(ctx, reinterpret_cast<const float4 *>(tris.data()), tri_floats / 4, &d_tris)) != SPK_OK ||
-        (rc = upload(ctx, instances.data(), instances.size(), &d_inst)) != SPK_OK ||
-        (rc = upload(ctx, dmeshes.data(), dmeshes.size(), &d_meshes)) != SPK_OK)
-    {
-        free_scene(ctx);
-        return rc;
-    }
-    ctx->d_pairs = d_pairs;
-    ctx->d_instances = d_inst;
+    // ---- one copy, one synchronize (host pointers are borrowed for this call only) ----
+    SPK_CUDA_TRY(cudaMemcpyAsync(dev, stage, plan.used, cudaMemcpyHostToDevice, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->d_pairs = reinterpret_cast<float4 *>(dev + off_pairs);
+    ctx->d_instances = reinterpret_cast<DInstance *>(dev + off_inst);
 
-    // ---- materials, textures, sky ----
-    std::vector<DTexture> dtex(s->num_textures);
-    for (uint32_t t = 0; t < s->num_textures; t++)
-    {
-        if ((rc = upload_texture(ctx, s->textures[t], dtex[t])) != SPK_OK)
-        {
-            free_scene(ctx);
-            return rc;
-        }
-    }
-    static_assert(sizeof(SpkMaterialDesc) == sizeof(DMaterial), "material ABI == device record");
-    DMaterial *d_mats = nullptr;
-    DTexture *d_tex = nullptr;
-    if ((rc = upload(ctx, reinterpret_cast<const DMaterial *>(s->materials), s->num_materials, &d_mats)) != SPK_OK ||
-        (rc = upload(ctx, dtex.data(), dtex.size(), &d_tex)) != SPK_OK)
-    {
-        free_scene(ctx);
-        return rc;
-    }
-    DSky sky{};
-    sky.has_sky = s->sky.has_sky;
-    sky.has_map = s->sky.has_sky ? s->sky.has_map : 0;
-    memcpy(sky.color, s->sky.color, 12);
-    if (sky.has_map)
-    {
-        for (int f = 0; f < 6; f++)
-        {
-            if ((rc = upload_texture(ctx, s->sky.faces[f], sky.faces[f])) != SPK_OK)
-            {
-                free_scene(ctx);
-                return rc;
-            }
-        }
-    }
-
-    ctx->scene.pairs = d_pairs;
-    ctx->scene.tris = d_tris;
-    ctx->scene.instances = d_inst;
-    ctx->scene.meshes = d_meshes;
-    ctx->scene.materials = d_mats;
-    ctx->scene.textures = d_tex;
+    ctx->scene.pairs = ctx->d_pairs;
+    ctx->scene.tris = reinterpret_cast<const float4 *>(dev + off_tris);
+    ctx->scene.instances = ctx->d_instances;
+    ctx->scene.meshes = reinterpret_cast<const DMesh *>(dev + off_meshes);
+    ctx->scene.materials = reinterpret_cast<const DMaterial *>(dev + off_mats);
+    ctx->scene.textures = reinterpret_cast<const DTexture *>(dev + off_tex);
     ctx->scene.num_instances = s->num_primitives;
     ctx->scene.cull_extent = s->world_extent > 0.f ? s->world_extent : 1.f;
     ctx->scene.sky = sky;
@@ -747,8 +850,7 @@ int spk_cuda_reset_accumulation(SpkContext *ctx)
     {
         return invalid("null context");
     }
-    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
-    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_accum, 0, size_t(ctx->width) * ctx->height * sizeof(float4), ctx->stream));
+    ctx->accum_clear_pending = true; // the next megakernel launch starts from zero; other consumers clear on demand
     ctx->accum_samples = 0;
     return SPK_OK;
 }
@@ -758,6 +860,11 @@ int spk_cuda_accum_device_ptr(SpkContext *ctx, void **device_ptr, size_t *bytes)
     if (!ctx || !device_ptr || !bytes)
     {
         return invalid("spk_cuda_accum_device_ptr: null argument");
+    }
+    int rc = ensure_accum_cleared(ctx); // an external reader (NCCL reduce) sees zeros after a reset
+    if (rc != SPK_OK)
+    {
+        return rc;
     }
     *device_ptr = ctx->d_accum;
     *bytes = size_t(ctx->width) * ctx->height * sizeof(float4);

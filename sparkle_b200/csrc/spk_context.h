@@ -17,7 +17,12 @@ struct SpkContext
 
     bool has_scene = false;
     spk::DScene scene{};
-    std::vector<void *> scene_allocs; // everything the current scene owns on the device
+    // every table of the current scene lives in one device arena, filled from one pinned staging buffer; both are kept
+    // across uploads and only grow (spk_api.cu)
+    void *d_arena = nullptr;
+    size_t arena_capacity = 0;
+    void *h_stage = nullptr;
+    size_t stage_capacity = 0;
     // kept for spk_cuda_update_instances
     std::vector<uint32_t> mesh_root_word;
     std::vector<uint32_t> material_class; // per material: 2 dielectric + 4 textured + 8 emissive (DInstance::shade_class)
@@ -34,6 +39,7 @@ struct SpkContext
     float4 *d_accum = nullptr; // W*H float4
     float4 *d_gbuf = nullptr;  // 2 x W*H float4 (colour + valid, first-hit normal), allocated on first denoised render
     uint32_t accum_samples = 0;
+    bool accum_clear_pending = false; // reset requested; done by the next megakernel launch for free, else by a memset
     uint32_t accum_mode = 0; // SpkAccumMode of the samples in d_accum
 
     unsigned long long *d_counters = nullptr; // 8 x u64
@@ -47,11 +53,16 @@ struct SpkContext
 
     void *d_resolve = nullptr;
     size_t resolve_capacity = 0;
+    void *h_resolve = nullptr; // pinned bounce buffer for pageable destinations (spk_cuda_resolve)
+    size_t h_resolve_capacity = 0;
+    cudaEvent_t resolve_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+    void *d_group_block = nullptr; // multi-GPU: flags + the root's gathered output, visible to peers (spk_group.cu)
 
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
     void *wf_block = nullptr;
     uint32_t wf_slots = 0;
-    int mega_variant = 2162; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
+    int mega_variant = 1162; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
     // explicit options (spk_cuda_set_option); nothing is read from the environment
     int opt_mega_form = 0;           // 0: use mega_variant
     uint32_t opt_wf_slots = 1u << 24; // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
@@ -89,10 +100,12 @@ cudaError_t prefer_small_carveout(Kernel kernel, size_t bytes_per_cta, int ctas,
     return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
 }
 
+// clears the accumulator now if spk_cuda_reset_accumulation left it pending (consumers other than the megakernels)
+int ensure_accum_cleared(SpkContext *ctx);
 // kernels (spk_trace.cu / spk_render.cu)
 int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags);
 int launch_render(SpkContext *ctx, const SpkRenderParams *params);
 int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *params);
 int launch_denoise_accumulate(SpkContext *ctx, uint32_t spatial, uint32_t accum_mode, uint32_t cumulated);
-int launch_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, uint32_t accum_mode, void *d_out);
+int copy_to_host(SpkContext *ctx, void *host_out, const void *d_src, size_t bytes);
 } // namespace spk

@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include "spk_shade.cuh"
 #include "spk_traverse.cuh"
 
@@ -38,6 +39,7 @@ struct RenderArgs
     uint32_t debug;
     uint32_t cumulated; // samples already in the accumulator (running-average mode)
     uint32_t cumulated_cap; // the camera's cap on that count (max_spp, CameraRenderProxy.cpp:70-73); 0xFFFFFFFF none
+    uint32_t fresh;         // 1: the accumulator was reset and not cleared yet - start from zero instead of reading it
 };
 
 // GBUF: one sample per pixel into a g-buffer instead of the accumulator (RenderPixel with spatial_denoise,
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
         const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
         const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
         const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
-        float4 acc = GBUF ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(j) * a.width + i];
+        float4 acc = (GBUF || a.fresh) ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(j) * a.width + i];
         V3 first_normal = mk(0.f, 0.f, 0.f);
         uint32_t stack[kThreadStack];
         for (uint32_t s = 0; s < a.sample_count; s++)
@@ -211,7 +213,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (in_image)
     {
-        acc = accum[size_t(j) * a.width + i];
+        acc = a.fresh ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(j) * a.width + i];
     }
     uint32_t stack[kThreadStack];
     uint32_t s = 0, bounce = 0;
@@ -394,20 +396,35 @@ template <int WARPS> constexpr size_t sorted_smem_bytes()
 // warp_trace_loop, lanes refilling from a shared-memory cursor). With only 256 rays per phase the loop's start-up, votes
 // and drain cost more than the idle lanes they save: TestScene 36.5 vs 23.4 ms per 32 spp, city 415 vs 327, room 233 vs
 // 159 (B200, same launch shapes).
-// PULL (the shipped form): the grid is persistent (SM count x CTAs per SM) and a column is not tied to a pixel. When a
-// column's pixel has all its samples the thread that shaded its last segment writes the pixel's sum to the accumulation
-// buffer and takes the NEXT PIXEL from a global counter (tile-linear order: 32 consecutive indices are one 8x4 tile), so
-// columns stay busy until the image is exhausted. Without it a CTA owned 512 pixels and lived until its SLOWEST pixel
-// had finished its samples (a pixel on glass needs up to 8x the segments of a sky pixel), holding its half of the SM's
-// threads and shared memory with a few live columns. A pixel's samples are still added in order by one thread at a
-// time, so the image is bit-identical to the owner forms. The column's pixel index lives in 16 bits of shared memory
-// plus 7 bits of the packed word (sample : 17 | pixel_hi : 7 | bounce : 8): < 2^23 pixels, < 2^17 samples per call.
-template <bool CULL, bool COUNT, int WARPS, int MINB, bool PULL>
+// PULL: the grid is persistent (SM count x CTAs per SM) and a column is not tied to a pixel. When a column's pixel has
+// all its samples the thread that shaded its last segment writes the pixel's sum to the accumulation buffer and takes the
+// NEXT PIXEL from the CTA's pixel pool, so columns stay busy until the image is exhausted. Without it a CTA owns 512
+// pixels and lives until its SLOWEST pixel has finished its samples (a pixel on glass needs up to 8x the segments of a
+// sky pixel), holding its half of the SM's threads and shared memory with a few live columns.
+// The pool is two chunks of T tile-linear pixel indices (32 consecutive indices are one 8x4 tile, T of them one strip
+// of tiles, the footprint of an owner-form CTA, so the CTA's rays stay as coherent as there) in shared memory; thread 0
+// swaps a fresh chunk in between the barriers of the sort when the first runs dry and keeps the NEXT chunk's global
+// atomicAdd in flight across a whole iteration. The first pulling form took every pixel with its own global atomicAdd
+// from inside the shading phase and then read the old accumulator value: two dependent ~1 us round trips on the CTA's
+// critical path in almost every iteration, and pixels from all over the image in one CTA - it measured 15 % SLOWER
+// than the owner form (TestScene 21.7 vs 18.8 ms per 32 spp). A pixel's samples are still added in order by one thread
+// at a time, so the image is bit-identical to the owner forms. The column's pixel index lives in 16 bits of shared
+// memory plus 7 bits of the packed word (sample : 17 | pixel_hi : 7 | bounce : 8): < 2^23 pixels, < 2^17 samples per call.
+// STABLE (MODE 2): the counting sort keeps the columns of a class in pixel order. Thread t looks at column t's class after
+// the trace: the lanes of a warp that agree (__match_any_sync) are one 8x4 tile's segments of that class, they take a
+// contiguous run of the class with ONE shared-memory atomicAdd by their first lane, and keep their order inside it. A warp
+// of the sorted order is then a few runs of tile neighbours: the rays it traces next are coherent (camera rays of
+// adjacent pixels, bounces off the same surface), its shared-memory columns are consecutive (the arbitrary order of the
+// per-thread atomicAdd form cost 2 of every 3 shared-memory wavefronts in bank conflicts), at the price of one more
+// barrier per iteration.
+template <bool CULL, bool COUNT, int WARPS, int MINB, int MODE>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
     render_sorted_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
                          unsigned long long *__restrict__ counters)
 {
+    constexpr bool PULL = MODE == 1, STABLE = MODE == 2;
     constexpr int T = WARPS * 32;
+    __shared__ uint8_t s_key[STABLE ? T : 1]; // STABLE: the shading class of every column's parked segment, 0xFF = no path
     extern __shared__ __align__(16) unsigned char s_dynamic[]; // sorted_smem_bytes<WARPS>()
     float *s_state = reinterpret_cast<float *>(s_dynamic);
     __shared__ uint32_t s_bin[2][32];
@@ -435,28 +452,29 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     uint32_t i = 0, j = 0;
     bool in_image;
     uint32_t pixels_done = 0;
+    __shared__ uint32_t s_pool[PULL ? 4 : 1]; // PULL: {next, end} of the chunk in use and of the reserve chunk
+    uint32_t prefetched = 0;                  // PULL, thread 0: base of the chunk after those, its atomicAdd in flight
+    auto clamp_px = [&](uint32_t p) { return p < total_px ? p : total_px; };
     if (PULL)
     {
-        // one atomic per warp: the warp's first 32 pixels are one tile (coherent camera rays, like the owner forms)
-        uint32_t p = 0;
-        in_image = false;
-        for (;;)
+        // three chunks to start with: one for the columns themselves, two for the pool
+        if (tid == 0)
         {
-            if (lane == 0)
-            {
-                p = atomicAdd(next_pixel, 32u);
-            }
-            p = __shfl_sync(0xffffffffu, p, 0) + lane;
-            if (p - lane >= total_px)
-            {
-                break;
-            }
+            const uint32_t base = atomicAdd(next_pixel, 3u * T);
+            s_pool[0] = clamp_px(base + T);
+            s_pool[1] = clamp_px(base + 2u * T);
+            s_pool[2] = clamp_px(base + 2u * T);
+            s_pool[3] = clamp_px(base + 3u * T);
+            s_total = base;
+            prefetched = atomicAdd(next_pixel, (uint32_t)T);
+        }
+        __syncthreads();
+        const uint32_t p = s_total + tid;
+        in_image = false;
+        if (p < total_px)
+        {
             pixel_of_index(p, i, j);
             in_image = i < a.width && j < a.height;
-            if (__any_sync(0xffffffffu, in_image))
-            {
-                break;
-            }
         }
         if (in_image)
         {
@@ -515,9 +533,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     };
     float *mine = s_state + tid; // the column this thread works on in the current iteration
     bool have = in_image && a.sample_count > 0u;
+    if (STABLE)
+    {
+        s_key[tid] = 0xFFu;
+    }
     if (in_image)
     {
-        const float4 acc = accum[size_t(j) * a.width + i];
+        const float4 acc = a.fresh ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(j) * a.width + i];
         mine[19 * T] = acc.x;
         mine[20 * T] = acc.y;
         mine[21 * T] = acc.z;
@@ -549,12 +571,39 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             mine[16 * T] = __uint_as_float(hit.inst);
             mine[17 * T] = __uint_as_float(hit.face);
             key = shade_class(sc, hit.inst);
-            pos = atomicAdd(&s_bin[parity][key], 1u);
+            if (STABLE)
+            {
+                s_key[mine - s_state] = (uint8_t)key;
+            }
+            else
+            {
+                pos = atomicAdd(&s_bin[parity][key], 1u);
+            }
         }
         __syncthreads();
-        if (tid < 32)
+        uint32_t sort_column = uint32_t(mine - s_state);
+        if (STABLE)
         {
-            uint32_t c = s_bin[parity][tid], incl = c;
+            // from here to the scatter thread t speaks for COLUMN t: tile neighbours of one class share an atomicAdd
+            key = s_key[tid];
+            have = key != 0xFFu;
+            sort_column = tid;
+            const uint32_t same = __match_any_sync(0xffffffffu, key);
+            const uint32_t rank = __popc(same & ((1u << lane) - 1u));
+            uint32_t base = 0;
+            if (have && rank == 0u)
+            {
+                base = atomicAdd(&s_bin[parity][key], (uint32_t)__popc(same));
+            }
+            pos = __shfl_sync(0xffffffffu, base, __ffs(same) - 1) + rank;
+            key &= 31u;
+            __syncthreads();
+        }
+        // every warp scans the 32 class counts itself (5 shuffles) instead of waiting for warp 0 behind another barrier
+        uint32_t n_live;
+        {
+            const uint32_t c = s_bin[parity][lane];
+            uint32_t incl = c;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1)
             {
@@ -564,22 +613,33 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                     incl += t;
                 }
             }
-            s_bin[parity][tid] = incl - c; // exclusive start of the class
-            s_bin[parity ^ 1u][tid] = 0;   // the other set was last read before the previous iteration's last barrier
-            if (tid == 31)
+            n_live = __shfl_sync(0xffffffffu, incl, 31);
+            const uint32_t start = __shfl_sync(0xffffffffu, incl - c, key); // exclusive start of this thread's class
+            if (have)
             {
-                s_total = incl;
+                s_sorted[start + pos] = (uint16_t)sort_column;
             }
         }
-        __syncthreads();
-        const uint32_t n_live = s_total;
+        if (tid < 32)
+        {
+            s_bin[parity ^ 1u][tid] = 0; // the other set was last read before the previous iteration's last barrier
+        }
+        if (PULL && tid == 0 && s_pool[0] >= s_pool[1])
+        {
+            // nobody takes pixels between the two barriers: the reserve chunk moves up, the prefetched one becomes the
+            // reserve, and the chunk after it is asked for now and used an iteration or more later
+            s_pool[0] = s_pool[2] < s_pool[3] ? s_pool[2] : s_pool[3];
+            s_pool[1] = s_pool[3];
+            s_pool[2] = clamp_px(prefetched);
+            s_pool[3] = clamp_px(prefetched + T);
+            if (prefetched < total_px)
+            {
+                prefetched = atomicAdd(next_pixel, (uint32_t)T);
+            }
+        }
         if (n_live == 0u)
         {
             break;
-        }
-        if (have)
-        {
-            s_sorted[s_bin[parity][key] + pos] = (uint16_t)(mine - s_state);
         }
         __syncthreads();
         parity ^= 1u;
@@ -716,15 +776,19 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                     have = false;
                     for (;;)
                     {
-                        const uint32_t p = atomicAdd(next_pixel, 1u);
-                        if (p >= total_px)
+                        uint32_t p = atomicAdd(&s_pool[0], 1u);
+                        if (p >= s_pool[1])
                         {
-                            break; // image exhausted: the column stays out of the next sort
+                            p = atomicAdd(&s_pool[2], 1u);
+                            if (p >= s_pool[3])
+                            {
+                                break; // image exhausted: the column stays out of the next sort
+                            }
                         }
                         pixel_of_index(p, pi, pj);
                         if (pi < a.width && pj < a.height)
                         {
-                            const float4 old = accum[size_t(pj) * a.width + pi];
+                            const float4 old = a.fresh ? make_float4(0.f, 0.f, 0.f, 0.f) : accum[size_t(pj) * a.width + pi];
                             src[19 * T] = old.x;
                             src[20 * T] = old.y;
                             src[21 * T] = old.z;
@@ -740,6 +804,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
                 else
                 {
                     have = false; // the pixel has all its samples: the column stays out of the next sort
+                    if (STABLE)
+                    {
+                        s_key[column] = 0xFFu;
+                    }
                 }
             }
         }
@@ -772,19 +840,19 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
 }
 
 // the sorted kernel's dynamic shared memory exceeds the 48 KiB default: opt in once per instantiation
-template <int W, int B, bool PULL> cudaError_t sorted_allow_smem(int carveout)
+template <int W, int B, int MODE> cudaError_t sorted_allow_smem(int carveout)
 {
     static cudaError_t done = [carveout] {
         cudaError_t e = cudaSuccess;
         const int bytes = (int)sorted_smem_bytes<W>();
         // static shared memory next to it: sorted index, (PULL) pixel index, two histogram sets, the total
-        const int fixed = W * 32 * 2 * (PULL ? 2 : 1) + 2 * 32 * 4 + 16;
+        const int fixed = W * 32 * 2 * (MODE == 1 ? 2 : 1) + (MODE == 2 ? W * 32 : 0) + 2 * 32 * 4 + 32;
 #define SPK_ALLOW(C, N)                                                                                                \
     if (e == cudaSuccess)                                                                                              \
-        e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B, PULL>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+        e = cudaFuncSetAttribute(render_sorted_kernel<C, N, W, B, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                  bytes);                                                                               \
     if (e == cudaSuccess)                                                                                              \
-        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B, PULL>, bytes + fixed, B, carveout);
+        e = spk::prefer_small_carveout(render_sorted_kernel<C, N, W, B, MODE>, bytes + fixed, B, carveout);
         SPK_ALLOW(true, false)
         SPK_ALLOW(false, false)
         SPK_ALLOW(true, true)
@@ -844,6 +912,59 @@ __global__ void resolve_kernel(const float4 *__restrict__ accum, uint32_t width,
 }
 } // namespace
 
+// Device -> caller's host buffer. Pinned destinations (spk_cuda_host_alloc, cudaHostAlloc, cudaHostRegister) take one
+// asynchronous copy at PCIe speed. A pageable destination goes through the context's pinned bounce buffer in 2 MiB
+// pieces, the host memcpy of piece k overlapping the DMA of piece k+1 (a plain pageable cudaMemcpy of the 16.6 MB fp16
+// frame was ~3 ms of every end-to-end step in round 1).
+int copy_to_host(SpkContext *ctx, void *host_out, const void *d_src, size_t bytes)
+{
+    cudaPointerAttributes attr{};
+    const bool pinned = cudaPointerGetAttributes(&attr, host_out) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError(); // an unregistered pointer is not an error here
+    if (pinned)
+    {
+        SPK_CUDA_TRY(cudaMemcpyAsync(host_out, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        return SPK_OK;
+    }
+    constexpr size_t kPiece = size_t(2) << 20;
+    constexpr int kRing = 4;
+    if (ctx->h_resolve_capacity < kPiece * kRing)
+    {
+        cudaFreeHost(ctx->h_resolve);
+        ctx->h_resolve = nullptr;
+        ctx->h_resolve_capacity = 0;
+        SPK_CUDA_TRY(cudaHostAlloc(&ctx->h_resolve, kPiece * kRing, cudaHostAllocDefault));
+        ctx->h_resolve_capacity = kPiece * kRing;
+        for (int k = 0; k < kRing; k++)
+        {
+            SPK_CUDA_TRY(cudaEventCreateWithFlags(&ctx->resolve_ev[k], cudaEventDisableTiming));
+        }
+    }
+    const size_t pieces = (bytes + kPiece - 1) / kPiece;
+    auto issue = [&](size_t k) -> cudaError_t {
+        const size_t at = k * kPiece, n = std::min(kPiece, bytes - at);
+        cudaError_t e = cudaMemcpyAsync(static_cast<uint8_t *>(ctx->h_resolve) + (k % kRing) * kPiece,
+                                        static_cast<const uint8_t *>(d_src) + at, n, cudaMemcpyDeviceToHost, ctx->stream);
+        return e != cudaSuccess ? e : cudaEventRecord(ctx->resolve_ev[k % kRing], ctx->stream);
+    };
+    for (size_t k = 0; k < pieces && k < size_t(kRing); k++)
+    {
+        SPK_CUDA_TRY(issue(k));
+    }
+    for (size_t k = 0; k < pieces; k++)
+    {
+        SPK_CUDA_TRY(cudaEventSynchronize(ctx->resolve_ev[k % kRing]));
+        const size_t at = k * kPiece, n = std::min(kPiece, bytes - at);
+        memcpy(static_cast<uint8_t *>(host_out) + at, static_cast<uint8_t *>(ctx->h_resolve) + (k % kRing) * kPiece, n);
+        if (k + kRing < pieces)
+        {
+            SPK_CUDA_TRY(issue(k + kRing));
+        }
+    }
+    return SPK_OK;
+}
+
 int launch_render(SpkContext *ctx, const SpkRenderParams *p)
 {
     RenderArgs a;
@@ -858,14 +979,33 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
     a.cumulated = ctx->accum_samples;
     a.cumulated_cap = p->cumulated_cap ? p->cumulated_cap : 0xFFFFFFFFu;
     a.debug = (p->flags >> 8) & 3u;
+    // spk_cuda_reset_accumulation only marks the accumulator: the megakernels write every pixel, so a fresh launch starts
+    // from zero in registers and the 33-133 MB clear never runs; the g-buffer path accumulates in another kernel
+    a.fresh = 0u;
+    if (ctx->accum_clear_pending)
+    {
+        if (p->flags & SPK_FLAG_SPATIAL_DENOISE)
+        {
+            int rc0 = ensure_accum_cleared(ctx);
+            if (rc0 != SPK_OK)
+            {
+                return rc0;
+            }
+        }
+        else
+        {
+            a.fresh = 1u;
+            ctx->accum_clear_pending = false;
+        }
+    }
     uint32_t tiles = ((a.width + kTileW - 1) / kTileW) * ((a.height + kTileH - 1) / kTileH);
     const DScene &scene = ctx->scene;
     const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
     // the form of the megakernel: SPK_OPT_MEGAKERNEL_FORM forces one (A/B runs), otherwise the one
-    // spk_cuda_choose_tracer measured fastest on this scene (2162 until measured)
+    // spk_cuda_choose_tracer measured fastest on this scene (1162 until measured)
     int phased = ctx->opt_mega_form > 0 ? ctx->opt_mega_form : ctx->mega_variant;
     const uint32_t total_px = tiles * 32u;
-    if (phased >= 2000 && (a.sample_count >= (1u << 17) || total_px >= (1u << 23)))
+    if (phased >= 2000 && phased < 3000 && (a.sample_count >= (1u << 17) || total_px >= (1u << 23)))
     {
         phased -= 1000; // the pulling form packs sample : 17 | pixel_hi : 7 | bounce : 8 into one word of a path slot
     }
@@ -878,36 +1018,40 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
         {
             SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
         }
-        if (phased >= 2000)
+        if (phased >= 2000 && phased < 3000)
         {
             // the pixel counter of the pulling form (counters[7]) starts every launch at zero
             SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), ctx->stream));
         }
         // form = 1000 + warps*10 + CTAs/SM: pixels owned by the CTA, one CTA per 16 tiles; 2000 + ...: persistent grid
-#define SPK_SORTED_LAUNCH(W, B, PULL, C, N)                                                                            \
-    render_sorted_kernel<C, N, W, B, PULL><<<(PULL) ? std::min<uint32_t>((tiles + W - 1) / W, uint32_t(sms) * B)       \
+#define SPK_SORTED_LAUNCH(W, B, MODE, C, N)                                                                            \
+    render_sorted_kernel<C, N, W, B, MODE><<<(MODE == 1) ? std::min<uint32_t>((tiles + W - 1) / W, uint32_t(sms) * B)  \
                                                     : (tiles + W - 1) / W,                                             \
                                              W * 32, sorted_smem_bytes<W>(), ctx->stream>>>(                           \
         scene, ctx->camera, a, ctx->d_accum, ctx->d_counters)
-#define SPK_SORTED_CASE(W, B, PULL)                                                                                    \
-    case (PULL ? 2000 : 1000) + W * 10 + B:                                                                            \
-        SPK_CUDA_TRY((sorted_allow_smem<W, B, PULL>(ctx->opt_carveout)));                                              \
+#define SPK_SORTED_CASE(W, B, MODE)                                                                                    \
+    case 1000 * (MODE + 1) + W * 10 + B:                                                                               \
+        SPK_CUDA_TRY((sorted_allow_smem<W, B, MODE>(ctx->opt_carveout)));                                              \
         if (!exact && !count)                                                                                          \
-            SPK_SORTED_LAUNCH(W, B, PULL, true, false);                                                                \
+            SPK_SORTED_LAUNCH(W, B, MODE, true, false);                                                                \
         else if (exact && !count)                                                                                      \
-            SPK_SORTED_LAUNCH(W, B, PULL, false, false);                                                               \
+            SPK_SORTED_LAUNCH(W, B, MODE, false, false);                                                               \
         else if (!exact)                                                                                               \
-            SPK_SORTED_LAUNCH(W, B, PULL, true, true);                                                                 \
+            SPK_SORTED_LAUNCH(W, B, MODE, true, true);                                                                 \
         else                                                                                                           \
-            SPK_SORTED_LAUNCH(W, B, PULL, false, true);                                                                \
+            SPK_SORTED_LAUNCH(W, B, MODE, false, true);                                                                \
         break;
         switch (phased)
         {
-            SPK_SORTED_CASE(8, 3, false)
-            SPK_SORTED_CASE(8, 4, false)
-            SPK_SORTED_CASE(16, 2, false)
-            SPK_SORTED_CASE(8, 4, true)
-            SPK_SORTED_CASE(16, 2, true)
+            SPK_SORTED_CASE(8, 3, 0)
+            SPK_SORTED_CASE(8, 4, 0)
+            SPK_SORTED_CASE(16, 2, 0)
+            SPK_SORTED_CASE(32, 1, 0)
+            SPK_SORTED_CASE(24, 1, 0)
+            SPK_SORTED_CASE(8, 4, 1)
+            SPK_SORTED_CASE(16, 2, 1)
+            SPK_SORTED_CASE(8, 4, 2)
+            SPK_SORTED_CASE(16, 2, 2)
         default:
             set_error("spk_cuda_render: unknown megakernel form (SPK_OPT_MEGAKERNEL_FORM)");
             return SPK_ERR_INVALID_ARGUMENT;
@@ -1095,11 +1239,12 @@ int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavef
     SPK_CUDA_TRY(cudaEventCreate(&e1));
     float ms[2] = {3.4e38f, 0.f};
     int rc = SPK_OK;
-    // candidates: the persistent sorted megakernel with 16 warps x 2 CTAs/SM and with 8 warps x 4 CTAs/SM, then the wavefront tracer
+    // candidates: the sorted megakernel with 16 warps x 2 CTAs/SM and with 8 warps x 4 CTAs/SM (pixels owned by the CTA; the
+    // pixel-pulling forms 2162 / 2084 measured 8-15 % slower on TestScene and room and stay as options), then the wavefront tracer
     // (the phased kernel has not won on any scene since the sorted form keeps its path slots in shared memory; it stays
     // as the fallback for probes, zero-bounce and > 255-bounce launches). A later form replaces the incumbent only when
     // it is more than 3 % faster: short timings of near-equal forms are noise.
-    static const int kForms[3] = {2162, 2084, -1};
+    static const int kForms[3] = {1162, 1084, -1};
     int best_form = kForms[0];
     for (int which = 0; which < 3 && rc == SPK_OK; which++)
     {
@@ -1140,7 +1285,7 @@ int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavef
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     // scratch use only: the accumulator and the counters go back to what they were
-    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_accum, 0, size_t(ctx->width) * ctx->height * sizeof(float4), ctx->stream));
+    ctx->accum_clear_pending = true;
     SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_counters, saved, sizeof(saved), cudaMemcpyHostToDevice, ctx->stream));
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     if (rc != SPK_OK)
@@ -1192,6 +1337,13 @@ int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, v
         SPK_CUDA_TRY(cudaMalloc(&ctx->d_resolve, need));
         ctx->resolve_capacity = need;
     }
+    {
+        int rc = ensure_accum_cleared(ctx);
+        if (rc != SPK_OK)
+        {
+            return rc;
+        }
+    }
     uint32_t n = total_samples ? total_samples : ctx->accum_samples;
     float divisor = ctx->accum_mode == SPK_ACCUM_SUM ? (float)(n ? n : 1u) : 1.f;
     float exposure = ctx->has_camera ? ctx->camera.exposure : 1.f;
@@ -1200,8 +1352,6 @@ int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, v
                                                     ctx->d_resolve);
     SPK_CUDA_TRY(cudaGetLastError());
     ctx->stats.kernel_launches++;
-    SPK_CUDA_TRY(cudaMemcpyAsync(host_out, ctx->d_resolve, need, cudaMemcpyDeviceToHost, ctx->stream));
-    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
-    return SPK_OK;
+    return copy_to_host(ctx, host_out, ctx->d_resolve, need);
 }
 } // extern "C"

@@ -448,6 +448,11 @@ int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *p)
         set_error("spk_cuda_render: parity probes (debug flags) are a megakernel feature");
         return SPK_ERR_UNSUPPORTED;
     }
+    int rc_clear = ensure_accum_cleared(ctx); // samples are added with atomics: a pending reset is cleared now
+    if (rc_clear != SPK_OK)
+    {
+        return rc_clear;
+    }
     WfArgs a;
     a.width = ctx->width;
     a.height = ctx->height;

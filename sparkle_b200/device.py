@@ -25,6 +25,9 @@ class CudaContext:
         if self.handle:
             self.lib.spk_cuda_destroy(self.handle)
             self.handle = A.CtxP()
+            for p in getattr(self, "_pinned", []):
+                self.lib.spk_cuda_host_free(p)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -57,15 +60,25 @@ class CudaContext:
                            cumulated_cap)
         A.check(self.lib.spk_cuda_render(self.handle, C.byref(p)))
 
-    def resolve(self, fmt=A.RESOLVE_LINEAR_F32, total_samples=0):
-        if fmt == A.RESOLVE_LINEAR_F32:
-            out = np.empty((self.height, self.width, 4), np.float32)
-        elif fmt == A.RESOLVE_TONEMAP_F16:
-            out = np.empty((self.height, self.width, 4), np.float16)
-        else:
-            out = np.empty((self.height, self.width, 4), np.uint8)
+    RESOLVE_DTYPES = {A.RESOLVE_LINEAR_F32: np.float32, A.RESOLVE_TONEMAP_F16: np.float16,
+                      A.RESOLVE_TONEMAP_SRGB8: np.uint8}
+
+    def resolve(self, fmt=A.RESOLVE_LINEAR_F32, total_samples=0, out=None):
+        """tone-map + read back; `out` may be a pinned frame buffer from pinned_frame() (one DMA, no staging)"""
+        if out is None:
+            out = np.empty((self.height, self.width, 4), self.RESOLVE_DTYPES[fmt])
         A.check(self.lib.spk_cuda_resolve(self.handle, fmt, total_samples, out.ctypes.data, out.nbytes))
         return out
+
+    def pinned_frame(self, fmt=A.RESOLVE_TONEMAP_F16):
+        """(H, W, 4) array over page-locked host memory (spk_cuda_host_alloc); freed with the context"""
+        dt = np.dtype(self.RESOLVE_DTYPES[fmt])
+        nbytes = self.height * self.width * 4 * dt.itemsize
+        p = C.c_void_p()
+        A.check(self.lib.spk_cuda_host_alloc(C.byref(p), nbytes))
+        self._pinned = getattr(self, "_pinned", []) + [p]
+        buf = (C.c_uint8 * nbytes).from_address(p.value)
+        return np.frombuffer(buf, dtype=dt).reshape(self.height, self.width, 4)
 
     def accum_ptr(self):
         p, n = C.c_void_p(), C.c_size_t()

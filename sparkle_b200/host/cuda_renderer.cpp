@@ -119,6 +119,31 @@ bool RenderConfig::Set(const std::string &name, const std::string &value)
     {
         ok = as_bool(spatial_denoise);
     }
+    else if (name == "gpus")
+    {
+        ok = as_u32(gpus) && gpus >= 1 && gpus <= 16;
+    }
+    else if (name == "gpu_devices")
+    {
+        // comma-separated CUDA device ordinals, one per GPU of `gpus`
+        gpu_devices.clear();
+        ok = !value.empty();
+        size_t at = 0;
+        while (ok && at <= value.size())
+        {
+            size_t comma = value.find(',', at);
+            const std::string item = value.substr(at, comma == std::string::npos ? std::string::npos : comma - at);
+            char *end = nullptr;
+            long v = strtol(item.c_str(), &end, 10);
+            ok = end != item.c_str() && *end == '\0' && v >= 0;
+            gpu_devices.push_back(int(v));
+            if (comma == std::string::npos)
+            {
+                break;
+            }
+            at = comma + 1;
+        }
+    }
     else if (name == "ssao")
     {
         ok = as_bool(use_ssao);
@@ -616,25 +641,47 @@ CudaRenderer::CudaRenderer(const RenderConfig &config, SceneProxy *scene, int de
 
 CudaRenderer::~CudaRenderer()
 {
-    if (ctx_)
+    if (group_)
     {
-        spk_cuda_destroy(ctx_);
+        spk_cuda_group_destroy(group_);
+    }
+    for (SpkContext *c : ctxs_)
+    {
+        spk_cuda_destroy(c);
     }
 }
 
 bool CudaRenderer::InitRenderResources()
 {
-    SpkCreateInfo info{};
-    info.abi_version = SPK_ABI_VERSION;
-    info.device = device_;
-    info.width = render_config_.image_width;
-    info.height = render_config_.image_height;
-    int rc = spk_cuda_create(&info, &ctx_);
-    if (rc != SPK_OK)
+    // one context per GPU of the `gpus` cvar; the first is the root (tone-mapping target and read-back)
+    uint32_t gpus = std::max(1u, render_config_.gpus);
+    if (gpus > 1 && render_config_.spatial_denoise)
     {
-        LogError(std::string("CudaRenderer: spk_cuda_create failed (") + std::to_string(rc) + "): " +
-                 spk_cuda_last_error());
-        ctx_ = nullptr;
+        LogError("CudaRenderer: spatial_denoise works on one accumulator: running on one GPU");
+        gpus = 1;
+    }
+    for (uint32_t g = 0; g < gpus; g++)
+    {
+        SpkCreateInfo info{};
+        info.abi_version = SPK_ABI_VERSION;
+        info.device = g < render_config_.gpu_devices.size() ? render_config_.gpu_devices[g] : device_ + int(g);
+        info.width = render_config_.image_width;
+        info.height = render_config_.image_height;
+        SpkContext *c = nullptr;
+        int rc = spk_cuda_create(&info, &c);
+        if (rc != SPK_OK)
+        {
+            LogError(std::string("CudaRenderer: spk_cuda_create failed (") + std::to_string(rc) + "): " +
+                     spk_cuda_last_error());
+            failed_ = true;
+            return false;
+        }
+        ctxs_.push_back(c);
+    }
+    ctx_ = ctxs_[0];
+    if (gpus > 1 && spk_cuda_group_create_local(ctxs_.data(), gpus, &group_) != SPK_OK)
+    {
+        LogError(std::string("CudaRenderer: spk_cuda_group_create_local failed: ") + spk_cuda_last_error());
         failed_ = true;
         return false;
     }
@@ -658,14 +705,29 @@ void CudaRenderer::Update()
     }
     const SpkSceneDesc &d = scene_render_proxy_->Desc();
     int rc = SPK_OK;
+    for (SpkContext *c : ctxs_) // the scene is replicated on every GPU
+    {
+        if (rc != SPK_OK)
+        {
+            break;
+        }
+        if (structural)
+        {
+            rc = spk_cuda_upload_scene(c, &d);
+        }
+        else if (moved)
+        {
+            rc = spk_cuda_update_instances(c, d.primitives, d.num_primitives, &d.tlas);
+            if (rc != SPK_OK)
+            {
+                // e.g. the rebuilt TLAS has more nodes than the uploaded one: a full upload always fits
+                rc = spk_cuda_upload_scene(c, &d);
+            }
+        }
+    }
     if (structural)
     {
-        rc = spk_cuda_upload_scene(ctx_, &d);
         scene_uploaded_ = rc == SPK_OK;
-    }
-    else if (moved)
-    {
-        rc = spk_cuda_update_instances(ctx_, d.primitives, d.num_primitives, &d.tlas);
     }
     if (rc != SPK_OK)
     {
@@ -686,8 +748,11 @@ void CudaRenderer::Render()
     int rc = SPK_OK;
     if (camera.NeedClear())
     {
-        rc = spk_cuda_set_camera(ctx_, &camera.Get());
-        rc = rc == SPK_OK ? spk_cuda_reset_accumulation(ctx_) : rc;
+        for (SpkContext *c : ctxs_)
+        {
+            rc = rc == SPK_OK ? spk_cuda_set_camera(c, &camera.Get()) : rc;
+            rc = rc == SPK_OK ? spk_cuda_reset_accumulation(c) : rc;
+        }
         camera.ClearPixels();
         dispatched_sample_count_ = 0;
     }
@@ -707,14 +772,38 @@ void CudaRenderer::Render()
     p.flags = render_config_.spatial_denoise ? SPK_FLAG_SPATIAL_DENOISE : 0u;
     // past max_spp the camera's cumulated count stays at the cap: an exponential moving average (CameraRenderProxy.cpp:70-73)
     p.cumulated_cap = render_config_.max_sample_per_pixel;
-    rc = rc == SPK_OK ? spk_cuda_render(ctx_, &p) : rc;
+    if (group_)
+    {
+        // gpus > 1: GPU g takes samples {g, g+G, ..} of this frame's n into its own SUM accumulator; the sums are combined
+        // when the frame is read (float association is the only difference from the running lerp, ~1e-7 relative).
+        // Past max_spp nothing more is added: the converged frame stays as it is.
+        const uint32_t G = uint32_t(ctxs_.size());
+        p.accum_mode = SPK_ACCUM_SUM;
+        p.cumulated_cap = 0;
+        p.flags |= SPK_FLAG_AUTO_TRACER;
+        for (uint32_t g = 0; g < G && rc == SPK_OK && remaining > 0; g++)
+        {
+            SpkRenderParams q = p;
+            q.first_sample = p.first_sample + g;
+            q.sample_stride = G;
+            q.sample_count = n > g ? (n - g + G - 1) / G : 0u;
+            rc = spk_cuda_render(ctxs_[g], &q);
+        }
+    }
+    else
+    {
+        rc = rc == SPK_OK ? spk_cuda_render(ctx_, &p) : rc;
+    }
     if (rc != SPK_OK)
     {
         LogError(std::string("CudaRenderer::Render: ") + spk_cuda_last_error());
         failed_ = true;
         return;
     }
-    dispatched_sample_count_ += n;
+    if (!(group_ && remaining == 0))
+    {
+        dispatched_sample_count_ += n; // (gpus > 1 adds nothing past max_spp: the divisor of the sums stays)
+    }
     camera.AccumulateSample(n);
     if (!screenshot_path_.empty() && IsReadyForAutoScreenshot())
     {
@@ -737,12 +826,22 @@ bool CudaRenderer::IsReadyForAutoScreenshot() const
 bool CudaRenderer::ReadLinear(std::vector<float> &out)
 {
     out.resize(size_t(render_config_.image_width) * render_config_.image_height * 4);
+    if (group_)
+    {
+        return spk_cuda_group_resolve(group_, SPK_RESOLVE_LINEAR_F32, dispatched_sample_count_, out.data(), out.size() * 4) ==
+               SPK_OK;
+    }
     return ctx_ && spk_cuda_resolve(ctx_, SPK_RESOLVE_LINEAR_F32, 0, out.data(), out.size() * 4) == SPK_OK;
 }
 
 bool CudaRenderer::ReadSrgb8(std::vector<uint8_t> &out)
 {
     out.resize(size_t(render_config_.image_width) * render_config_.image_height * 4);
+    if (group_)
+    {
+        return spk_cuda_group_resolve(group_, SPK_RESOLVE_TONEMAP_SRGB8, dispatched_sample_count_, out.data(), out.size()) ==
+               SPK_OK;
+    }
     return ctx_ && spk_cuda_resolve(ctx_, SPK_RESOLVE_TONEMAP_SRGB8, 0, out.data(), out.size()) == SPK_OK;
 }
 

@@ -58,6 +58,10 @@ struct RenderConfig
     bool spatial_denoise = true; // code default; the packaged config sets false (resources/packed/config/config.json:17)
     bool use_ssao = false;
     bool use_prepass = false;
+    // cuda pipeline only (no counterpart in RenderConfig.cpp:13-48): GPUs of this box the frame's samples are split over
+    // (scene replicated, spp interleaved, spk_cuda_group_resolve combines), and which devices (default: device, device+1, ..)
+    uint32_t gpus = 1;
+    std::vector<int> gpu_devices;
 
     [[nodiscard]] bool IsCPURenderMode() const { return pipeline == Pipeline::Cpu; }
     [[nodiscard]] bool IsCudaRenderMode() const { return pipeline == Pipeline::Cuda; }
@@ -224,7 +228,9 @@ protected:
 
 private:
     int device_;
-    SpkContext *ctx_ = nullptr;
+    SpkContext *ctx_ = nullptr;            // the root context (== ctxs_[0])
+    std::vector<SpkContext *> ctxs_;       // one per GPU of the `gpus` cvar
+    SpkGroup *group_ = nullptr;            // gpus > 1: fused reduce + resolve over peer memory (include/spk_cuda.h)
     uint32_t dispatched_sample_count_ = 0;
     bool scene_uploaded_ = false;
     bool failed_ = false;

@@ -93,3 +93,29 @@ def test_gltf_scene_through_the_host_app(tmp_path, oracle):
     assert rel.mean() <= 1e-3, rel.mean()
     assert (gpu[..., :3].std() > 0.01)  # an actual picture, not a constant
     a.close()
+
+
+def test_gpus_cvar_splits_samples_and_equals_one_gpu(oracle):
+    """--gpus 2: one context per GPU in ONE process (local SpkGroup), samples interleaved, frames combined by the fused
+    reduce + resolve kernel. The frame equals the 1-GPU frame (float association only) and the CPU path tracer's. On a
+    1-GPU box both contexts sit on device 0 (--gpu_devices 0,0): the local group orders its kernels with stream events."""
+    import torch
+    w, h, spp = 96, 64, 10
+    ndev = torch.cuda.device_count()
+    devs = "0,1" if ndev >= 2 else "0,0"
+    common = f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 4 --spatial_denoise false"
+    one = app.HostApp(common)
+    assert one.run(100) == 3
+    img1 = one.read_linear()
+    two = app.HostApp(common + f" --gpus 2 --gpu_devices {devs}")
+    assert two.run(100) == 3 and two.cumulated_samples == spp
+    img2 = two.read_linear()
+    assert np.allclose(img1, img2, rtol=2e-6, atol=2e-6), float(np.abs(img1 - img2).max())
+    ref, _ = oracle.render(two.scene, two.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
+    assert rel_err(img2, ref) <= 1e-3
+    # frames past max_spp add nothing in the multi-GPU form: the frame stays
+    two.frame()
+    two.frame()
+    assert np.array_equal(two.read_linear(), img2)
+    one.close()
+    two.close()

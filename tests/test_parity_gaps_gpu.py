@@ -214,7 +214,7 @@ def test_running_average_past_max_spp(oracle):
     for _ in range(frames):
         happ.frame()
     host_img = happ.read_linear()
-    hdesc, hcam = happ.scene(), happ.camera()
+    hdesc, hcam = happ.scene, happ.camera
     href, _ = oracle.render(hdesc, hcam, w, h, 0, frames, accum_mode=A.ACCUM_RUNNING_AVERAGE, cumulated_cap=cap)
     mh = PR.report("a15_host_app_past_cap", host_img, href)
     happ.close()
