@@ -150,6 +150,7 @@ HOST_SYMBOLS = {
     "spk_host_last_error": (C.c_char_p, []),
     "spk_host_app_frame": (C.c_int, [C.c_void_p]),
     "spk_host_app_run": (C.c_int, [C.c_void_p, u32]),
+    "spk_host_app_render_frame": (C.c_int, [C.c_void_p]),
     "spk_host_app_scene": (C.POINTER(SceneDesc), [C.c_void_p]),
     "spk_host_app_camera": (C.POINTER(Camera), [C.c_void_p]),
     "spk_host_app_cumulated_samples": (u32, [C.c_void_p]),

@@ -36,6 +36,10 @@ class HostApp:
     def frame(self):
         return self.lib.spk_host_app_frame(self.handle)
 
+    def render_frame(self):
+        """the reference's frame (Tick, Render, ready flag): keeps rendering past max_spp"""
+        return self.lib.spk_host_app_render_frame(self.handle)
+
     def run(self, max_frames=1 << 20):
         return self.lib.spk_host_app_run(self.handle, max_frames)
 

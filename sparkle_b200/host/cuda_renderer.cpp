@@ -1165,6 +1165,18 @@ int spk_host_app_frame(SpkHostApp *app)
     return 0;
 }
 
+int spk_host_app_render_frame(SpkHostApp *app)
+{
+    // the reference's order exactly (RenderFramework.cpp:153-158): Tick, Render, then the ready flag. Past max_spp every
+    // such frame lerps one more sample in with weight cap/(cap+1) (CameraRenderProxy.cpp:70-73). spk_host_app_frame
+    // checks BEFORE rendering so that spk_host_app_run stops with exactly max_spp samples: the reference's screenshot is
+    // requested asynchronously and holds max_spp + k samples, k >= 1 depending on thread timing.
+    app->renderer->Tick();
+    app->renderer->Render();
+    app->frames++;
+    return app->renderer->IsReadyForAutoScreenshot() ? 1 : 0;
+}
+
 int spk_host_app_run(SpkHostApp *app, uint32_t max_frames)
 {
     uint32_t start = app->frames;

@@ -257,6 +257,8 @@ const char *spk_host_last_error(void);
 /* RenderFramework::RenderLoop body (RenderFramework.cpp:146-162): Tick + Render; returns 1 when ready for the auto screenshot */
 int spk_host_app_frame(SpkHostApp *app);
 int spk_host_app_run(SpkHostApp *app, uint32_t max_frames); /* frames rendered until ready */
+/* Tick + Render unconditionally, then the ready flag: the reference's frame, which keeps rendering past max_spp */
+int spk_host_app_render_frame(SpkHostApp *app);
 const SpkSceneDesc *spk_host_app_scene(SpkHostApp *app);
 const SpkCamera *spk_host_app_camera(SpkHostApp *app);
 uint32_t spk_host_app_cumulated_samples(SpkHostApp *app);

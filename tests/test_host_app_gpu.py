@@ -114,8 +114,8 @@ def test_gpus_cvar_splits_samples_and_equals_one_gpu(oracle):
     ref, _ = oracle.render(two.scene, two.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
     assert rel_err(img2, ref) <= 1e-3
     # frames past max_spp add nothing in the multi-GPU form: the frame stays
-    two.frame()
-    two.frame()
+    two.render_frame()
+    two.render_frame()
     assert np.array_equal(two.read_linear(), img2)
     one.close()
     two.close()

@@ -212,7 +212,7 @@ def test_running_average_past_max_spp(oracle):
     happ = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {cap} --spp 1 --spatial_denoise false "
                        "--scene testscene")
     for _ in range(frames):
-        happ.frame()
+        happ.render_frame()
     host_img = happ.read_linear()
     hdesc, hcam = happ.scene, happ.camera
     href, _ = oracle.render(hdesc, hcam, w, h, 0, frames, accum_mode=A.ACCUM_RUNNING_AVERAGE, cumulated_cap=cap)
