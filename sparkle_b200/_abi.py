@@ -162,6 +162,9 @@ HOST_SYMBOLS = {
     "spk_host_scene_load_gltf": (C.c_void_p, [C.c_char_p, C.c_int]),
     "spk_host_scene_desc": (C.POINTER(SceneDesc), [C.c_void_p]),
     "spk_host_scene_free": (None, [C.c_void_p]),
+    "spk_host_usd_probe": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint64)]),
+    "spk_host_scene_load_usd": (C.c_void_p, [C.c_char_p, u32, u32]),
+    "spk_host_scene_camera": (C.POINTER(Camera), [C.c_void_p]),
     "spk_host_gltf_probe": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_uint64)]),
     # host/ref_math.h: Transform / orbit camera in the reference's float operation order
     "spk_host_trs": (None, [fp, fp, fp, fp, fp]),

@@ -15,6 +15,7 @@
 
 #include "bvh_builder.h"
 #include "gltf_loader.h"
+#include "usd_loader.h"
 
 namespace sparkle_cuda
 {
@@ -1117,12 +1118,24 @@ SpkHostApp *spk_host_app_create(const char *args, int device)
         return nullptr;
     }
     const bool gltf = scene_name.size() > 5 && scene_name.compare(scene_name.size() - 5, 5, ".gltf") == 0;
-    if (scene_name != "testscene" && scene_name != "empty" && !gltf)
+    const bool usd = scene_name.size() > 5 && scene_name.compare(scene_name.size() - 5, 5, ".usda") == 0;
+    if (scene_name != "testscene" && scene_name != "empty" && !gltf && !usd)
     {
-        LogError("unknown scene '" + scene_name + "' (testscene, empty or a .gltf path)");
+        LogError("unknown scene '" + scene_name + "' (testscene, empty, a .gltf path or a .usda path)");
         return nullptr;
     }
-    if (gltf)
+    if (usd)
+    {
+        // SceneManager::LoadScene -> USDLoader::Load (the default scene of the app is resources/packed/TestScene.usda):
+        // sky and camera come from the file when it has a DomeLight / Camera, else the app defaults
+        app->scene.SetSky(Vec3{0.5f, 0.7f, 1.0f});
+        app->scene.GetCamera().SetupOrbit(Vec3{0, 0, 0}, 25.f, 10.f, -20.f);
+        if (!LoadUsd(scene_name, app->scene))
+        {
+            return nullptr;
+        }
+    }
+    else if (gltf)
     {
         // SceneManager::LoadScene -> GLTFLoader::Load (AppFramework.cpp:200-205: a failed load logs and fails init)
         if (!LoadGltf(scene_name, app->scene, nullptr, gltf_options))

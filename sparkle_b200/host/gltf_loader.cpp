@@ -1043,12 +1043,6 @@ extern "C" int spk_host_gltf_probe(const char *path, int instancing, uint64_t *s
     return 0;
 }
 
-// a scene loaded without a renderer (CPU tests feed its SpkSceneDesc to the oracle)
-struct SpkHostScene
-{
-    sparkle_cuda::RenderConfig config;
-    sparkle_cuda::SceneProxy scene;
-};
 
 extern "C" SpkHostScene *spk_host_scene_load_gltf(const char *path, int instancing)
 {

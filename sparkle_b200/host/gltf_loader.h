@@ -51,13 +51,19 @@ bool LoadGltf(const std::string &path, SceneProxy &scene, GltfStats *stats = nul
 bool DecodePng(const uint8_t *data, size_t size, std::vector<uint8_t> &rgba, uint32_t &width, uint32_t &height);
 } // namespace sparkle_cuda
 
+// a scene loaded without a renderer (CPU tests feed its SpkSceneDesc to the oracle); shared with usd_loader.cpp
+struct SpkHostScene
+{
+    sparkle_cuda::RenderConfig config;
+    sparkle_cuda::SceneProxy scene;
+};
+
 extern "C"
 {
 /* tests / headless driver: "--scene file.gltf" goes through LoadGltf; this probe loads a file into a scratch scene and
  * returns the counters (7 x u64 in GltfStats order), or -1 */
 int spk_host_gltf_probe(const char *path, int instancing, uint64_t *stats7);
 /* a glTF scene without a renderer: its flattened description (TLAS built) for the oracle; NULL on failure */
-typedef struct SpkHostScene SpkHostScene;
 SpkHostScene *spk_host_scene_load_gltf(const char *path, int instancing);
 const SpkSceneDesc *spk_host_scene_desc(SpkHostScene *scene);
 void spk_host_scene_free(SpkHostScene *scene);

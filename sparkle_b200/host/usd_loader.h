@@ -24,6 +24,7 @@
 #ifndef SPARKLE_CUDA_USD_LOADER_H
 #define SPARKLE_CUDA_USD_LOADER_H
 #include "cuda_renderer.h"
+#include "gltf_loader.h" // SpkHostScene
 
 #include <string>
 
@@ -53,8 +54,7 @@ extern "C"
 int spk_host_usd_probe(const char *path, uint64_t *stats9);
 /* a USD scene without a renderer: flattened description (TLAS built) for the oracle and its camera; NULL on failure.
  * Freed with spk_host_scene_free, read with spk_host_scene_desc (gltf_loader.h). */
-struct SpkHostScene;
-struct SpkHostScene *spk_host_scene_load_usd(const char *path, uint32_t width, uint32_t height);
-const SpkCamera *spk_host_scene_camera(struct SpkHostScene *scene);
+SpkHostScene *spk_host_scene_load_usd(const char *path, uint32_t width, uint32_t height);
+const SpkCamera *spk_host_scene_camera(SpkHostScene *scene);
 }
 #endif
