@@ -47,6 +47,9 @@ typedef enum SpkStatus {
  * prim_count; prim_count==0 marks an inner node whose children are nodes[first_id], nodes[first_id+1];
  * node 0 is the root. `node_stride` is 28 (the raw library struct) or 32 (padded). `prim_ids` maps
  * leaf slots to primitive indices (bvh_.prim_ids; 8-byte size_t in the library, 4-byte also accepted).
+ * nodes == NULL with num_nodes == 0: the tree is BUILT ON THE DEVICE by spk_cuda_upload_scene (an LBVH: Morton sort,
+ * Karras hierarchy, bottom-up fit, leaves of <= 4 triangles / 1 primitive; csrc/spk_build.cu) and can be read back with
+ * spk_cuda_download_bvh.
  */
 typedef struct SpkBvhNode {
     float bounds[6];
@@ -255,9 +258,24 @@ int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream);
 /* SceneRenderProxy::Update/UpdateBVH consumer (SceneRenderProxy.cpp:195-297): flattens TLAS/BLAS, triangle,
  * attribute, material and texture tables into aligned device buffers. Replaces any previous scene. */
 int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *scene);
-/* PrimitiveChangeType::Update (SceneRenderProxy.cpp:212-230): new transforms + rebuilt TLAS, BLAS kept. */
+/* PrimitiveChangeType::Update (SceneRenderProxy.cpp:212-230): new transforms + rebuilt TLAS, BLAS kept. tlas == NULL (or
+ * a descriptor with nodes == NULL): the TLAS is rebuilt on the device from the new transforms. */
 int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitives, uint32_t num_primitives,
                               const SpkBvhDesc *tlas);
+/* Any tree of the uploaded scene (mesh index, or SPK_BVH_TLAS) back in the bvh::v2 node layout + prim_ids, so that a CPU
+ * consumer (the oracle, the reference's traversal) walks the topology the device walks. Call with NULL arrays for sizes. */
+#define SPK_BVH_TLAS 0xFFFFFFFFu
+int spk_cuda_download_bvh(SpkContext *ctx, uint32_t mesh, SpkBvhNode *nodes_out, uint32_t node_capacity,
+                          uint32_t *num_nodes_out, uint32_t *prim_ids_out, uint32_t prim_capacity, uint32_t *num_prims_out);
+typedef struct SpkBuildInfo {
+    uint32_t device_built; /* 1: built by spk_build.cu, 0: handed in by the caller */
+    uint32_t num_nodes;
+    uint32_t num_prims;
+    uint32_t depth;   /* device-built trees only */
+    double sah_cost;  /* device-built trees only: (sum of inner areas + sum of leaf area * count) / root area */
+    double build_ms;  /* device time of the build (CUDA events) */
+} SpkBuildInfo;
+int spk_cuda_get_build_info(SpkContext *ctx, uint32_t mesh, SpkBuildInfo *out);
 /* CameraRenderProxy::OnTransformDirty (CameraRenderProxy.cpp:113-136). */
 int spk_cuda_set_camera(SpkContext *ctx, const SpkCamera *camera);
 /* CPURenderer::Render's NeedClear branch (CPURenderer.cpp:128-137). */
@@ -323,7 +341,8 @@ typedef enum SpkOption {
     SPK_OPT_TRACE_VOTE = 3,      /* ray-batch kernel: lanes waiting in a leaf state that switch the warp to it (4, 6, 8, 12, 16; default 6) */
     SPK_OPT_SMEM_CARVEOUT = 4,   /* percent of the SM's shared-memory/L1 array asked for as shared memory; -1 driver
                                     default, -2 (default) the smallest that holds the resident CTAs */
-    SPK_OPT_VERBOSE = 5          /* 1: spk_cuda_choose_tracer prints its timings to stderr */
+    SPK_OPT_VERBOSE = 5,         /* 1: spk_cuda_choose_tracer prints its timings to stderr */
+    SPK_OPT_BUILD_MAX_LEAF = 6   /* triangles per leaf of device-built BLAS (1..15, default 4) */
 } SpkOption;
 int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value);
 

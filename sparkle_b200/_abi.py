@@ -18,7 +18,8 @@ FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY, FLAG_A
 FLAG_SPATIAL_DENOISE = 32
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
 (OPT_MEGAKERNEL_FORM, OPT_WAVEFRONT_SLOTS, OPT_WAVEFRONT_CHUNK, OPT_TRACE_VOTE, OPT_SMEM_CARVEOUT,
- OPT_VERBOSE) = range(6)
+ OPT_VERBOSE, OPT_BUILD_MAX_LEAF) = range(7)
+BVH_TLAS = 0xFFFFFFFF
 
 u32, i32, f32, u64 = C.c_uint32, C.c_int32, C.c_float, C.c_uint64
 fp = C.POINTER(f32)
@@ -92,6 +93,11 @@ class CreateInfo(C.Structure):
     _fields_ = [("abi_version", u32), ("device", i32), ("width", u32), ("height", u32)]
 
 
+class BuildInfo(C.Structure):
+    _fields_ = [("device_built", u32), ("num_nodes", u32), ("num_prims", u32), ("depth", u32), ("sah_cost", C.c_double),
+                ("build_ms", C.c_double)]
+
+
 CtxP = C.c_void_p
 GroupP = C.c_void_p
 PEER_HANDLE_BYTES = 192
@@ -113,6 +119,8 @@ CUDA_SYMBOLS = {
     "spk_cuda_set_option": (C.c_int, [CtxP, u32, C.c_int64]),
     "spk_cuda_upload_scene": (C.c_int, [CtxP, C.POINTER(SceneDesc)]),
     "spk_cuda_update_instances": (C.c_int, [CtxP, C.POINTER(PrimitiveDesc), u32, C.POINTER(BvhDesc)]),
+    "spk_cuda_download_bvh": (C.c_int, [CtxP, u32, C.POINTER(BvhNode), u32, u32p, u32p, u32, u32p]),
+    "spk_cuda_get_build_info": (C.c_int, [CtxP, u32, C.POINTER(BuildInfo)]),
     "spk_cuda_set_camera": (C.c_int, [CtxP, C.POINTER(Camera)]),
     "spk_cuda_reset_accumulation": (C.c_int, [CtxP]),
     "spk_cuda_render": (C.c_int, [CtxP, C.POINTER(RenderParams)]),

@@ -6,6 +6,7 @@
 #include "spk_context.h"
 
 #include <cfloat>
+#include <cstddef>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -174,6 +175,18 @@ uint32_t root_word(const SpkBvhDesc &d, uint32_t pair_base, uint32_t leaf_base)
     HostNode n = read_node(d, 0);
     uint32_t count = n.index & 15u, first = n.index >> 4;
     return count == 0 ? ((pair_base + (first - 1) / 2) << 4) : (((leaf_base + first) << 4) | count);
+}
+
+// SpkBvhDesc with nodes == NULL: the tree is built on the device (spk_build.cu)
+bool build_on_device(const SpkBvhDesc &d)
+{
+    return d.nodes == nullptr && d.num_nodes == 0;
+}
+
+// pair slots a mesh takes in the one pair array: what its host tree has, or the upper bound of a device build
+uint32_t mesh_pair_slots(const SpkMeshDesc &md)
+{
+    return build_on_device(md.blas) ? md.num_faces : (md.blas.num_nodes - 1) / 2;
 }
 
 // ---- scene arena ----
@@ -351,6 +364,7 @@ int spk_cuda_destroy(SpkContext *ctx)
     cudaFree(ctx->d_resolve);
     cudaFree(ctx->wf_block);
     cudaFree(ctx->d_group_block);
+    cudaFree(ctx->d_build_scratch);
     cudaFree(ctx->d_gbuf);
     if (ctx->ev0)
     {
@@ -414,6 +428,13 @@ int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value)
     case SPK_OPT_VERBOSE:
         ctx->opt_verbose = value != 0;
         return SPK_OK;
+    case SPK_OPT_BUILD_MAX_LEAF:
+        if (value < 1 || value > 15)
+        {
+            return invalid("spk_cuda_set_option: leaf size of device-built BLAS must be in [1, 15]");
+        }
+        ctx->opt_build_max_leaf = uint32_t(value);
+        return SPK_OK;
     default:
         return invalid("spk_cuda_set_option: unknown option");
     }
@@ -457,6 +478,81 @@ int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream)
 }
 } // extern "C"
 
+namespace spk
+{
+// TLAS::Build on the device: world boxes of the primitives (AABB::TransformTo of the mesh bounds, SceneRenderProxy.cpp:41-47;
+// centre +- radius for spheres) -> LBVH with one primitive per leaf -> instances in the order of the sorted leaves.
+int rebuild_tlas_on_device(SpkContext *ctx, const SpkPrimitiveDesc *prims, uint32_t n)
+{
+    std::vector<float> boxes(size_t(n) * 6);
+    for (uint32_t p = 0; p < n; p++)
+    {
+        const SpkPrimitiveDesc &pd = prims[p];
+        float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        if (pd.kind == SPK_PRIM_SPHERE)
+        {
+            const float r = std::sqrt(pd.radius2);
+            for (int a = 0; a < 3; a++)
+            {
+                lo[a] = pd.fwd[4 * a + 3] - r;
+                hi[a] = pd.fwd[4 * a + 3] + r;
+            }
+        }
+        else
+        {
+            const float *b = ctx->mesh_trees[pd.mesh].root_bounds;
+            for (int corner = 0; corner < 8; corner++)
+            {
+                const float c[3] = {corner & 4 ? b[3] : b[0], corner & 2 ? b[4] : b[1], corner & 1 ? b[5] : b[2]};
+                for (int a = 0; a < 3; a++)
+                {
+                    const float *row = pd.fwd + 4 * a;
+                    const float w = ((row[0] * c[0] + row[1] * c[1]) + row[2] * c[2]) + row[3];
+                    lo[a] = std::min(lo[a], w);
+                    hi[a] = std::max(hi[a], w);
+                }
+            }
+        }
+        memcpy(&boxes[size_t(p) * 6], lo, 12);
+        memcpy(&boxes[size_t(p) * 6 + 3], hi, 12);
+    }
+    SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_tlas_boxes, boxes.data(), boxes.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    DeviceBuildResult res;
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = device_build_lbvh(ctx, nullptr, nullptr, ctx->d_tlas_boxes, n, 1u, ctx->d_pairs, ctx->tlas_tree.pair_base, 0u,
+                               nullptr, &res);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
+    std::vector<uint32_t> order(n);
+    SPK_CUDA_TRY(cudaMemcpyAsync(order.data(), ctx->build_ids, size_t(n) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    std::vector<DInstance> instances(n);
+    for (uint32_t k = 0; k < n; k++)
+    {
+        fill_instance(instances[k], prims[order[k]], order[k], ctx->mesh_root_word, ctx->material_class);
+    }
+    SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_instances, instances.data(), instances.size() * sizeof(DInstance),
+                                 cudaMemcpyHostToDevice, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    SpkContext::TreeInfo &t = ctx->tlas_tree;
+    t.num_pairs = res.num_pairs;
+    t.root_word = res.root_word;
+    t.depth = res.depth;
+    t.sah_cost = res.sah_cost;
+    t.build_ms = ms;
+    t.device_built = true;
+    t.num_prims = n;
+    memcpy(t.root_bounds, res.root_bounds, 24);
+    ctx->scene.tlas_root = res.root_word;
+    return SPK_OK;
+}
+} // namespace spk
+
 /* ---- device scene builder ------------------------------------------------------------------------------------- */
 extern "C"
 {
@@ -494,6 +590,10 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
                 return;
             }
         }
+        if (build_on_device(md.blas))
+        {
+            return; // BLAS::Build runs on the device (spk_build.cu)
+        }
         if (validate_bvh(md.blas, md.num_faces, "") != SPK_OK)
         {
             mesh_status[m] = 3;
@@ -507,7 +607,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
                            : mesh_status[m] == 2 ? "spk_cuda_upload_scene: vertex index out of range"
                                                  : "spk_cuda_upload_scene: malformed BLAS");
         }
-        total_pairs += (s->meshes[m].blas.num_nodes - 1) / 2;
+        total_pairs += mesh_pair_slots(s->meshes[m]);
         total_tris += s->meshes[m].num_faces;
     }
     for (uint32_t p = 0; p < s->num_primitives; p++)
@@ -535,13 +635,22 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
             return invalid("spk_cuda_upload_scene: material type");
         }
     }
+    const bool tlas_on_device = s->num_primitives && build_on_device(s->tlas);
     if (s->num_primitives)
     {
-        if ((rc = validate_bvh(s->tlas, s->num_primitives, "spk_cuda_upload_scene: malformed TLAS")) != SPK_OK)
+        if (tlas_on_device)
         {
-            return rc;
+            total_pairs += s->num_primitives; // upper bound of a rebuilt TLAS (n - 1 pairs)
         }
-        total_pairs += (s->tlas.num_nodes - 1) / 2;
+        else
+        {
+            if ((rc = validate_bvh(s->tlas, s->num_primitives, "spk_cuda_upload_scene: malformed TLAS")) != SPK_OK)
+            {
+                return rc;
+            }
+            // a later spk_cuda_update_instances may rebuild the TLAS on the device: leave room for its n - 1 pairs
+            total_pairs += std::max<uint32_t>((s->tlas.num_nodes - 1) / 2, s->num_primitives);
+        }
     }
     if (total_pairs >= (1ull << 28) || total_tris >= (1ull << 28))
     {
@@ -577,7 +686,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     const size_t off_tex = plan.add(size_t(s->num_textures) * sizeof(DTexture));
     struct MeshOffsets
     {
-        size_t normals, tangents, indices, uvs;
+        size_t normals, tangents, indices, uvs, vertices;
     };
     std::vector<MeshOffsets> mesh_off(s->num_meshes);
     for (uint32_t m = 0; m < s->num_meshes; m++)
@@ -587,7 +696,9 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         mesh_off[m].tangents = plan.add(size_t(md.num_vertices) * 16);
         mesh_off[m].indices = plan.add(size_t(md.num_faces) * 12);
         mesh_off[m].uvs = md.uvs ? plan.add(size_t(md.num_vertices) * 8) : 0;
+        mesh_off[m].vertices = build_on_device(md.blas) ? plan.add(size_t(md.num_vertices) * 12) : 0;
     }
+    const size_t off_boxes = plan.add(size_t(s->num_primitives) * 24); // world boxes of a device-built TLAS
     auto texture_bytes = [](const SpkTextureDesc &t) { return size_t(t.width) * t.height * texel_bytes(t.format); };
     std::vector<size_t> tex_off(s->num_textures);
     for (uint32_t t = 0; t < s->num_textures; t++)
@@ -612,6 +723,8 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     float *const tris = reinterpret_cast<float *>(stage + off_tris);
     memset(pairs + size_t(total_pairs) * 16, 0, 64);
     ctx->mesh_root_word.assign(s->num_meshes, 0);
+    ctx->mesh_trees.assign(s->num_meshes, SpkContext::TreeInfo{});
+    ctx->tlas_tree = SpkContext::TreeInfo{};
     uint32_t pair_base = 0, tri_base = 0;
     // work items: one flatten_pairs per mesh, the triangle records in chunks of 64 Ki faces, and plain copies of the
     // attribute / texture arrays in chunks of 4 MiB
@@ -637,12 +750,31 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     for (uint32_t m = 0; m < s->num_meshes; m++)
     {
         const SpkMeshDesc &md = s->meshes[m];
-        items.push_back(Item{m, pair_base, tri_base, 0, 0});
-        for (uint32_t b = 0; b < md.num_faces; b += 65536u)
+        SpkContext::TreeInfo &tree = ctx->mesh_trees[m];
+        tree.pair_base = pair_base;
+        tree.leaf_base = tri_base;
+        tree.num_prims = md.num_faces;
+        tree.device_built = build_on_device(md.blas);
+        if (tree.device_built)
         {
-            items.push_back(Item{m, pair_base, tri_base, b, std::min(md.num_faces, b + 65536u)});
+            add_copy(md.vertices, mesh_off[m].vertices, size_t(md.num_vertices) * 12);
         }
-        pair_base += (md.blas.num_nodes - 1) / 2;
+        else
+        {
+            items.push_back(Item{m, pair_base, tri_base, 0, 0});
+            for (uint32_t b = 0; b < md.num_faces; b += 65536u)
+            {
+                items.push_back(Item{m, pair_base, tri_base, b, std::min(md.num_faces, b + 65536u)});
+            }
+            tree.num_pairs = (md.blas.num_nodes - 1) / 2;
+            const HostNode root = read_node(md.blas, 0);
+            for (int a = 0; a < 3; a++)
+            {
+                tree.root_bounds[a] = root.bounds[2 * a];
+                tree.root_bounds[3 + a] = root.bounds[2 * a + 1];
+            }
+        }
+        pair_base += mesh_pair_slots(md);
         tri_base += md.num_faces;
         add_copy(md.normals, mesh_off[m].normals, size_t(md.num_vertices) * 12);
         add_copy(md.tangents, mesh_off[m].tangents, size_t(md.num_vertices) * 16);
@@ -697,6 +829,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         {
             flatten_pairs(md.blas, it.pair_base, it.tri_base, pairs + size_t(it.pair_base) * 16);
             ctx->mesh_root_word[it.mesh] = root_word(md.blas, it.pair_base, it.tri_base);
+            ctx->mesh_trees[it.mesh].root_word = ctx->mesh_root_word[it.mesh];
             return;
         }
         for (uint32_t k = it.begin; k < it.end; k++)
@@ -732,14 +865,32 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     // ---- TLAS pairs + instances in TLAS leaf order (SceneRenderProxy.cpp:59-68) ----
     DInstance *const instances = reinterpret_cast<DInstance *>(stage + off_inst);
     ctx->scene = DScene{};
-    if (s->num_primitives)
+    ctx->tlas_tree.pair_base = pair_base;
+    ctx->tlas_tree.num_prims = s->num_primitives;
+    bool meshes_on_device = false;
+    for (const SpkContext::TreeInfo &t : ctx->mesh_trees)
+    {
+        meshes_on_device |= t.device_built;
+    }
+    if (s->num_primitives && !tlas_on_device)
     {
         flatten_pairs(s->tlas, pair_base, 0, pairs + size_t(pair_base) * 16);
         ctx->scene.tlas_root = root_word(s->tlas, pair_base, 0);
-        for (uint32_t k = 0; k < s->num_primitives; k++)
+        ctx->tlas_tree.root_word = ctx->scene.tlas_root;
+        ctx->tlas_tree.num_pairs = (s->tlas.num_nodes - 1) / 2;
+        const HostNode troot = read_node(s->tlas, 0);
+        for (int a = 0; a < 3; a++)
         {
-            uint32_t prim = read_prim_id(s->tlas, k);
-            fill_instance(instances[k], s->primitives[prim], prim, ctx->mesh_root_word, ctx->material_class);
+            ctx->tlas_tree.root_bounds[a] = troot.bounds[2 * a];
+            ctx->tlas_tree.root_bounds[3 + a] = troot.bounds[2 * a + 1];
+        }
+        if (!meshes_on_device)
+        {
+            for (uint32_t k = 0; k < s->num_primitives; k++)
+            {
+                uint32_t prim = read_prim_id(s->tlas, k);
+                fill_instance(instances[k], s->primitives[prim], prim, ctx->mesh_root_word, ctx->material_class);
+            }
         }
     }
     ctx->pair_capacity = uint32_t(total_pairs);
@@ -750,7 +901,61 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->d_pairs = reinterpret_cast<float4 *>(dev + off_pairs);
     ctx->d_instances = reinterpret_cast<DInstance *>(dev + off_inst);
+    ctx->d_tlas_boxes = reinterpret_cast<float *>(dev + off_boxes);
 
+    // ---- BLAS::Build on the device for the meshes that came without a tree (MeshRenderProxy.cpp:31-65) ----
+    for (uint32_t m = 0; m < s->num_meshes; m++)
+    {
+        SpkContext::TreeInfo &tree = ctx->mesh_trees[m];
+        if (!tree.device_built)
+        {
+            continue;
+        }
+        DeviceBuildResult res;
+        cudaEvent_t e0 = ctx->ev0, e1 = ctx->ev1;
+        SPK_CUDA_TRY(cudaEventRecord(e0, ctx->stream));
+        rc = device_build_lbvh(ctx, reinterpret_cast<const float *>(dev + mesh_off[m].vertices),
+                               reinterpret_cast<const uint32_t *>(dev + mesh_off[m].indices), nullptr, s->meshes[m].num_faces,
+                               ctx->opt_build_max_leaf, ctx->d_pairs, tree.pair_base, tree.leaf_base,
+                               reinterpret_cast<float4 *>(dev + off_tris) + size_t(tree.leaf_base) * 3, &res);
+        if (rc != SPK_OK)
+        {
+            return rc;
+        }
+        SPK_CUDA_TRY(cudaEventRecord(e1, ctx->stream));
+        SPK_CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        tree.build_ms = ms;
+        tree.num_pairs = res.num_pairs;
+        tree.root_word = res.root_word;
+        tree.depth = res.depth;
+        tree.sah_cost = res.sah_cost;
+        memcpy(tree.root_bounds, res.root_bounds, 24);
+        ctx->mesh_root_word[m] = res.root_word;
+    }
+    // ---- TLAS::Build on the device (SceneRenderProxy.cpp:31-69), or instances that waited for device-built BLAS roots ----
+    if (tlas_on_device)
+    {
+        if ((rc = rebuild_tlas_on_device(ctx, s->primitives, s->num_primitives)) != SPK_OK)
+        {
+            return rc;
+        }
+    }
+    else if (s->num_primitives && meshes_on_device)
+    {
+        std::vector<DInstance> late(s->num_primitives);
+        for (uint32_t k = 0; k < s->num_primitives; k++)
+        {
+            uint32_t prim = read_prim_id(s->tlas, k);
+            fill_instance(late[k], s->primitives[prim], prim, ctx->mesh_root_word, ctx->material_class);
+        }
+        SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_instances, late.data(), late.size() * sizeof(DInstance), cudaMemcpyHostToDevice,
+                                     ctx->stream));
+        SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    }
+
+    const uint32_t tlas_root_keep = ctx->scene.tlas_root;
     ctx->scene.pairs = ctx->d_pairs;
     ctx->scene.tris = reinterpret_cast<const float4 *>(dev + off_tris);
     ctx->scene.instances = ctx->d_instances;
@@ -758,6 +963,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     ctx->scene.materials = reinterpret_cast<const DMaterial *>(dev + off_mats);
     ctx->scene.textures = reinterpret_cast<const DTexture *>(dev + off_tex);
     ctx->scene.num_instances = s->num_primitives;
+    ctx->scene.tlas_root = tlas_root_keep;
     ctx->scene.cull_extent = s->world_extent > 0.f ? s->world_extent : 1.f;
     ctx->scene.sky = sky;
     ctx->has_scene = true;
@@ -768,7 +974,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
 int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitives, uint32_t num_primitives,
                               const SpkBvhDesc *tlas)
 {
-    if (!ctx || !primitives || !tlas)
+    if (!ctx || !primitives)
     {
         return invalid("spk_cuda_update_instances: null argument");
     }
@@ -780,6 +986,34 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
     if (num_primitives != ctx->instance_capacity || num_primitives == 0)
     {
         return invalid("spk_cuda_update_instances: primitive count changed (use spk_cuda_upload_scene)");
+    }
+    for (uint32_t p = 0; p < num_primitives; p++)
+    {
+        if (primitives[p].kind > SPK_PRIM_SPHERE || primitives[p].material >= ctx->material_class.size() ||
+            (primitives[p].kind == SPK_PRIM_MESH && primitives[p].mesh >= ctx->mesh_root_word.size()))
+        {
+            return invalid("spk_cuda_update_instances: primitive references a missing mesh or material");
+        }
+    }
+    if (!tlas || build_on_device(*tlas))
+    {
+        // TLAS == NULL: rebuilt on the device from the new transforms (SceneRenderProxy.cpp:212-230, 269-297)
+        SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+        int rc0 = rebuild_tlas_on_device(ctx, primitives, num_primitives);
+        if (rc0 != SPK_OK)
+        {
+            return rc0;
+        }
+        float extent = 0.f;
+        for (float b : ctx->tlas_tree.root_bounds)
+        {
+            extent = std::max(extent, std::fabs(b));
+        }
+        if (extent > 0.f && std::isfinite(extent))
+        {
+            ctx->scene.cull_extent = extent;
+        }
+        return SPK_OK;
     }
     int rc = validate_bvh(*tlas, num_primitives, "spk_cuda_update_instances: malformed TLAS");
     if (rc != SPK_OK)
@@ -817,6 +1051,9 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
                                  cudaMemcpyHostToDevice, ctx->stream));
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     ctx->scene.tlas_root = root_word(*tlas, ctx->tlas_pair_base, 0);
+    ctx->tlas_tree.root_word = ctx->scene.tlas_root;
+    ctx->tlas_tree.num_pairs = tlas_pairs;
+    ctx->tlas_tree.device_built = false;
     // the t-culling slack is sized from the world extent (spk_traverse.cuh): primitives may have moved outside the
     // bounds of the upload, so take it again from the rebuilt TLAS root (= the world AABB)
     const HostNode root = read_node(*tlas, 0);
@@ -825,10 +1062,108 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
     {
         extent = std::max(extent, std::fabs(b));
     }
+    for (int a = 0; a < 3; a++)
+    {
+        ctx->tlas_tree.root_bounds[a] = root.bounds[2 * a];
+        ctx->tlas_tree.root_bounds[3 + a] = root.bounds[2 * a + 1];
+    }
     if (extent > 0.f && std::isfinite(extent))
     {
         ctx->scene.cull_extent = extent;
     }
+    return SPK_OK;
+}
+
+int spk_cuda_download_bvh(SpkContext *ctx, uint32_t mesh, SpkBvhNode *nodes_out, uint32_t node_capacity,
+                          uint32_t *num_nodes_out, uint32_t *prim_ids_out, uint32_t prim_capacity, uint32_t *num_prims_out)
+{
+    if (!ctx || !num_nodes_out || !num_prims_out)
+    {
+        return invalid("spk_cuda_download_bvh: null argument");
+    }
+    if (!ctx->has_scene)
+    {
+        set_error("spk_cuda_download_bvh: no scene uploaded");
+        return SPK_ERR_NO_SCENE;
+    }
+    const bool is_tlas = mesh == SPK_BVH_TLAS;
+    if (!is_tlas && mesh >= ctx->mesh_trees.size())
+    {
+        return invalid("spk_cuda_download_bvh: no such mesh");
+    }
+    const SpkContext::TreeInfo &t = is_tlas ? ctx->tlas_tree : ctx->mesh_trees[mesh];
+    *num_nodes_out = 1 + 2 * t.num_pairs;
+    *num_prims_out = t.num_prims;
+    if (!nodes_out && !prim_ids_out)
+    {
+        return SPK_OK; // size query
+    }
+    if (!nodes_out || !prim_ids_out || node_capacity < *num_nodes_out || prim_capacity < t.num_prims)
+    {
+        return invalid("spk_cuda_download_bvh: output arrays too small (call with NULL arrays for the sizes)");
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    std::vector<float> pairs(size_t(t.num_pairs) * 16);
+    if (t.num_pairs)
+    {
+        SPK_CUDA_TRY(cudaMemcpyAsync(pairs.data(), ctx->d_pairs + size_t(t.pair_base) * 4, pairs.size() * 4,
+                                     cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    // primitive ids in leaf order: the face index in a triangle record, the primitive index in an instance record
+    if (t.num_prims)
+    {
+        const uint8_t *src = is_tlas ? reinterpret_cast<const uint8_t *>(ctx->d_instances) + offsetof(DInstance, prim)
+                                     : reinterpret_cast<const uint8_t *>(ctx->scene.tris) + size_t(t.leaf_base) * 48 + 12;
+        SPK_CUDA_TRY(cudaMemcpy2DAsync(prim_ids_out, 4, src, is_tlas ? sizeof(DInstance) : 48, 4, t.num_prims,
+                                       cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    // absolute index words back to the bvh::v2 form: children of an inner node at ids 1 + 2 * slot, leaves relative
+    auto relative = [&](uint32_t word) {
+        const uint32_t count = word & 15u, first = word >> 4;
+        return count == 0 ? ((1u + 2u * (first - t.pair_base)) << 4) : (((first - t.leaf_base) << 4) | count);
+    };
+    memset(nodes_out, 0, sizeof(SpkBvhNode) * size_t(*num_nodes_out));
+    for (int a = 0; a < 3; a++)
+    {
+        nodes_out[0].bounds[2 * a] = t.root_bounds[a];
+        nodes_out[0].bounds[2 * a + 1] = t.root_bounds[3 + a];
+    }
+    nodes_out[0].index = relative(t.root_word);
+    for (uint32_t k = 0; k < 2 * t.num_pairs; k++)
+    {
+        const float *rec = pairs.data() + size_t(k) * 8;
+        memcpy(nodes_out[1 + k].bounds, rec, 24);
+        uint32_t word;
+        memcpy(&word, rec + 6, 4);
+        nodes_out[1 + k].index = relative(word);
+    }
+    return SPK_OK;
+}
+
+int spk_cuda_get_build_info(SpkContext *ctx, uint32_t mesh, SpkBuildInfo *out)
+{
+    if (!ctx || !out)
+    {
+        return invalid("spk_cuda_get_build_info: null argument");
+    }
+    if (!ctx->has_scene)
+    {
+        set_error("spk_cuda_get_build_info: no scene uploaded");
+        return SPK_ERR_NO_SCENE;
+    }
+    const bool is_tlas = mesh == SPK_BVH_TLAS;
+    if (!is_tlas && mesh >= ctx->mesh_trees.size())
+    {
+        return invalid("spk_cuda_get_build_info: no such mesh");
+    }
+    const SpkContext::TreeInfo &t = is_tlas ? ctx->tlas_tree : ctx->mesh_trees[mesh];
+    out->device_built = t.device_built ? 1u : 0u;
+    out->num_nodes = 1 + 2 * t.num_pairs;
+    out->num_prims = t.num_prims;
+    out->depth = t.depth;
+    out->sah_cost = t.sah_cost;
+    out->build_ms = t.build_ms;
     return SPK_OK;
 }
 

@@ -3,6 +3,7 @@
 #include "../../include/spk_cuda.h"
 #include "spk_device.cuh"
 
+#include <algorithm>
 #include <cstdlib>
 #include <cuda_runtime.h>
 #include <string>
@@ -57,6 +58,23 @@ struct SpkContext
     size_t h_resolve_capacity = 0;
     cudaEvent_t resolve_ev[4] = {nullptr, nullptr, nullptr, nullptr};
 
+    // device BVH builder (spk_build.cu): scratch kept across builds; build_ids = sorted primitive ids of the last build
+    void *d_build_scratch = nullptr;
+    size_t build_scratch_capacity = 0;
+    uint32_t *build_ids = nullptr;
+    float *d_tlas_boxes = nullptr; // world boxes of the primitives, in the scene arena
+    uint32_t opt_build_max_leaf = 4; // BLAS leaves of device-built trees (the TLAS always gets one primitive per leaf)
+    // where every tree of the current scene lives (spk_cuda_download_bvh, spk_cuda_update_instances, build reports)
+    struct TreeInfo
+    {
+        uint32_t pair_base = 0, num_pairs = 0, leaf_base = 0, num_prims = 0, root_word = 0, depth = 0;
+        float root_bounds[6] = {0, 0, 0, 0, 0, 0}; // min.xyz, max.xyz
+        double sah_cost = 0.0;
+        double build_ms = 0.0;
+        bool device_built = false;
+    };
+    std::vector<TreeInfo> mesh_trees;
+    TreeInfo tlas_tree;
     void *d_group_block = nullptr; // multi-GPU: flags + the root's gathered output, visible to peers (spk_group.cu)
 
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
@@ -102,6 +120,16 @@ cudaError_t prefer_small_carveout(Kernel kernel, size_t bytes_per_cta, int ctas,
 
 // clears the accumulator now if spk_cuda_reset_accumulation left it pending (consumers other than the megakernels)
 int ensure_accum_cleared(SpkContext *ctx);
+struct DeviceBuildResult
+{
+    uint32_t num_pairs, root_word, depth;
+    float root_bounds[6]; // min.xyz, max.xyz
+    double sah_cost;
+};
+// spk_build.cu: LBVH over triangles (d_vertices / d_indices; leaf-ordered records to d_tris) or over boxes (d_boxes_in)
+int device_build_lbvh(SpkContext *ctx, const float *d_vertices, const uint32_t *d_indices, const float *d_boxes_in, uint32_t n,
+                      uint32_t max_leaf, float4 *d_pairs, uint32_t pair_base, uint32_t leaf_base, float4 *d_tris,
+                      DeviceBuildResult *out);
 // kernels (spk_trace.cu / spk_render.cu)
 int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *d_hits, uint32_t flags);
 int launch_render(SpkContext *ctx, const SpkRenderParams *params);

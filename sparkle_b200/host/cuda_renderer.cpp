@@ -120,6 +120,10 @@ bool RenderConfig::Set(const std::string &name, const std::string &value)
     {
         ok = as_bool(spatial_denoise);
     }
+    else if (name == "device_tlas")
+    {
+        ok = as_bool(device_tlas);
+    }
     else if (name == "gpus")
     {
         ok = as_u32(gpus) && gpus >= 1 && gpus <= 16;
@@ -718,7 +722,7 @@ void CudaRenderer::Update()
         }
         else if (moved)
         {
-            rc = spk_cuda_update_instances(c, d.primitives, d.num_primitives, &d.tlas);
+            rc = spk_cuda_update_instances(c, d.primitives, d.num_primitives, render_config_.device_tlas ? nullptr : &d.tlas);
             if (rc != SPK_OK)
             {
                 // e.g. the rebuilt TLAS has more nodes than the uploaded one: a full upload always fits

@@ -61,6 +61,9 @@ struct RenderConfig
     // cuda pipeline only (no counterpart in RenderConfig.cpp:13-48): GPUs of this box the frame's samples are split over
     // (scene replicated, spp interleaved, spk_cuda_group_resolve combines), and which devices (default: device, device+1, ..)
     uint32_t gpus = 1;
+    // PrimitiveChangeType::Update: rebuild the TLAS on the device (spk_cuda_update_instances with tlas == NULL) instead
+    // of uploading the host-rebuilt one
+    bool device_tlas = false;
     std::vector<int> gpu_devices;
 
     [[nodiscard]] bool IsCPURenderMode() const { return pipeline == Pipeline::Cpu; }

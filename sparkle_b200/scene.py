@@ -48,9 +48,31 @@ class HostBvh:
         return d
 
 
+class DeviceBvh:
+    """a tree read back from the device (spk_cuda_download_bvh) in the bvh::v2 layout: what the kernels traverse"""
+
+    def __init__(self, ctx, mesh):
+        lib = ctx.lib
+        n, p = A.u32(), A.u32()
+        A.check(lib.spk_cuda_download_bvh(ctx.handle, mesh, None, 0, C.byref(n), None, 0, C.byref(p)))
+        self.nodes = np.zeros((n.value, 8), np.uint32)
+        self.prim_ids = np.zeros(max(1, p.value), np.uint32)[:p.value]
+        A.check(lib.spk_cuda_download_bvh(ctx.handle, mesh, C.cast(self.nodes.ctypes.data, C.POINTER(A.BvhNode)), n.value,
+                                          C.byref(n), C.cast(self.prim_ids.ctypes.data, A.u32p), p.value, C.byref(p)))
+        info = A.BuildInfo()
+        A.check(lib.spk_cuda_get_build_info(ctx.handle, mesh, C.byref(info)))
+        self.info = {k: getattr(info, k) for k, _ in A.BuildInfo._fields_}
+        self.depth, self.sah = info.depth, info.sah_cost
+
+    desc = HostBvh.desc
+
+
 class SceneBuilder:
-    def __init__(self, max_leaf=4):
+    def __init__(self, max_leaf=4, device_build=False):
+        """device_build: meshes and the TLAS come WITHOUT trees (SpkBvhDesc.nodes == NULL): spk_cuda_upload_scene builds
+        them on the device (csrc/spk_build.cu); adopt_device_trees() reads them back for CPU consumers"""
         self.max_leaf = max_leaf
+        self.device_build = device_build
         self.meshes = []      # MeshData
         self.blas = []        # HostBvh
         self.materials = []   # dict
@@ -88,7 +110,7 @@ class SceneBuilder:
 
     def add_mesh(self, mesh: MeshData):
         self.meshes.append(mesh)
-        self.blas.append(HostBvh.from_mesh(mesh, self.max_leaf))
+        self.blas.append(None if self.device_build else HostBvh.from_mesh(mesh, self.max_leaf))
         return len(self.meshes) - 1
 
     # ---- primitives (registration order == SpkHit.prim) ----
@@ -149,7 +171,7 @@ class SceneBuilder:
             md.indices = m.indices.ctypes.data_as(A.u32p)
             md.num_vertices = len(m.vertices)
             md.num_faces = m.num_faces
-            md.blas = b.desc()
+            md.blas = b.desc() if b is not None else A.BvhDesc()
         d.num_meshes = len(self.meshes)
         d.meshes = marr
         parr = self.primitive_array()
@@ -173,8 +195,10 @@ class SceneBuilder:
         d.num_textures = len(self.textures)
         d.textures = tarr
         if self.prims:
-            self.build_tlas()
-            d.tlas = self.tlas.desc()
+            if not self.device_build:
+                self.build_tlas()
+            if self.tlas is not None:
+                d.tlas = self.tlas.desc()
             lo, hi = self.world_bounds()
             d.world_extent = float(max(np.abs(lo).max(), np.abs(hi).max()))
         d.sky.has_sky = self.sky["has_sky"]
@@ -189,6 +213,26 @@ class SceneBuilder:
         keep += [marr, parr, matarr, tarr]
         self.desc = d
         return d
+
+    def adopt_device_trees(self, ctx):
+        """after ctx.upload_scene(self.finalize()) of a device_build scene: read every tree back and return a description
+        that carries them, so the oracle traverses the topology the device built"""
+        self.blas = [DeviceBvh(ctx, m) for m in range(len(self.meshes))]
+        self.tlas = DeviceBvh(ctx, A.BVH_TLAS) if self.prims else None
+        self.device_build = False
+        try:
+            return self.finalize_keep_trees()
+        finally:
+            self.device_build = True
+
+    def finalize_keep_trees(self):
+        tlas = self.tlas
+        build = self.build_tlas
+        self.build_tlas = lambda: tlas  # keep the downloaded TLAS instead of building one on the host
+        try:
+            return self.finalize()
+        finally:
+            self.build_tlas = build
 
     def stats(self):
         return dict(meshes=len(self.meshes), primitives=len(self.prims),

@@ -75,6 +75,23 @@ def test_primitive_move_restarts_accumulation(oracle):
     a.close()
 
 
+def test_primitive_move_with_device_side_tlas_rebuild(oracle):
+    """8f-4: --device_tlas true -> PrimitiveChange::Update rebuilds the TLAS on the device (LBVH over the instances' world
+    boxes); the closest hit does not depend on the topology, so the image still matches the oracle on the host's scene"""
+    w, h, spp = 96, 64, 4
+    a = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 1 --spatial_denoise false "
+                    "--device_tlas true")
+    a.run(100)
+    before = a.read_linear()
+    a.move_primitive(3, (2.0, -1.0, 3.5))
+    a.run(100)
+    after = a.read_linear()
+    assert np.abs(after[..., :3] - before[..., :3]).max() > 0.05
+    ref, _ = oracle.render(a.scene, a.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
+    assert rel_err(after, ref) <= 1e-3
+    a.close()
+
+
 def test_gltf_scene_through_the_host_app(tmp_path, oracle):
     """8f-1: --scene file.gltf -> GLTFLoader semantics -> CudaRenderer; the image equals the oracle's on the app's own
     scene description"""
