@@ -342,7 +342,9 @@ typedef enum SpkOption {
     SPK_OPT_SMEM_CARVEOUT = 4,   /* percent of the SM's shared-memory/L1 array asked for as shared memory; -1 driver
                                     default, -2 (default) the smallest that holds the resident CTAs */
     SPK_OPT_VERBOSE = 5,         /* 1: spk_cuda_choose_tracer prints its timings to stderr */
-    SPK_OPT_BUILD_MAX_LEAF = 6   /* triangles per leaf of device-built BLAS (1..15, default 4) */
+    SPK_OPT_BUILD_MAX_LEAF = 6,  /* triangles per leaf of device-built BLAS (1..15, default 4) */
+    SPK_OPT_TRACE_SMEM_TOP = 7   /* ray-batch kernel: pairs of the hottest tree's top levels (the TLAS, else the first BLAS)
+                                    staged in shared memory: 0 (default, measured), 64, 128, 256, 512 */
 } SpkOption;
 int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value);
 

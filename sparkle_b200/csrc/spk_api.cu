@@ -152,17 +152,61 @@ int validate_bvh(const SpkBvhDesc &d, uint32_t expected_prims, const char *what)
     return SPK_OK;
 }
 
-// nodes[1..] -> 64-byte pairs appended at pair slot `pair_base`; leaf words offset by `leaf_base`
-void flatten_pairs(const SpkBvhDesc &d, uint32_t pair_base, uint32_t leaf_base, float *dst)
+// nodes[1..] -> 64-byte pairs appended at pair slot `pair_base`; leaf words offset by `leaf_base`.
+// By default a pair keeps the builder's depth-first slot. level_order_top (set while SPK_OPT_TRACE_SMEM_TOP is on): slots are
+// handed out LEVEL BY LEVEL for the first kTopLevels levels, so the top of the tree is one contiguous run that the ray-batch
+// kernel can stage in shared memory (measured and rejected: DESIGN.md 4.1). Index words are absolute, so the visit order of a
+// ray does not depend on where a pair is stored.
+constexpr uint32_t kTopLevels = 10;
+
+void flatten_pairs(const SpkBvhDesc &d, uint32_t pair_base, uint32_t leaf_base, float *dst, bool level_order_top = false)
 {
+    const uint32_t num_pairs = (d.num_nodes - 1) / 2;
+    std::vector<uint8_t> level(num_pairs, uint8_t(kTopLevels));
+    if (level_order_top)
+    {
+        // level of a pair = depth of its parent node (the pair of the root's children is level 0)
+        std::vector<std::pair<uint32_t, uint32_t>> todo;
+        todo.emplace_back(0u, 0u);
+        while (!todo.empty())
+        {
+            auto [id, depth] = todo.back();
+            todo.pop_back();
+            const uint32_t index = read_node(d, id).index;
+            if ((index & 15u) == 0u)
+            {
+                const uint32_t first = index >> 4;
+                level[(first - 1) / 2] = uint8_t(std::min(depth, kTopLevels));
+                if (depth + 1 < kTopLevels)
+                {
+                    todo.emplace_back(first, depth + 1);
+                    todo.emplace_back(first + 1, depth + 1);
+                }
+            }
+        }
+    }
+    uint32_t cursor[kTopLevels + 2] = {};
+    for (uint32_t q = 0; q < num_pairs; q++)
+    {
+        cursor[level[q] + 1]++;
+    }
+    for (uint32_t l = 0; l <= kTopLevels; l++)
+    {
+        cursor[l + 1] += cursor[l];
+    }
+    std::vector<uint32_t> slot_of(num_pairs);
+    for (uint32_t q = 0; q < num_pairs; q++)
+    {
+        slot_of[q] = cursor[level[q]]++;
+    }
     auto rewrite = [&](uint32_t index) {
         uint32_t count = index & 15u, first = index >> 4;
-        return count == 0 ? ((pair_base + (first - 1) / 2) << 4) : (((leaf_base + first) << 4) | count);
+        return count == 0 ? ((pair_base + slot_of[(first - 1) / 2]) << 4) : (((leaf_base + first) << 4) | count);
     };
     for (uint32_t i = 1; i < d.num_nodes; i++)
     {
         HostNode n = read_node(d, i);
-        float *o = dst + size_t(i - 1) * 8;
+        float *o = dst + (size_t(slot_of[(i - 1) / 2]) * 2 + ((i - 1) & 1u)) * 8;
         memcpy(o, n.bounds, 24);
         uint32_t w = rewrite(n.index);
         memcpy(o + 6, &w, 4);
@@ -428,6 +472,13 @@ int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value)
     case SPK_OPT_VERBOSE:
         ctx->opt_verbose = value != 0;
         return SPK_OK;
+    case SPK_OPT_TRACE_SMEM_TOP:
+        if (value != 0 && value != 64 && value != 128 && value != 256 && value != 512)
+        {
+            return invalid("spk_cuda_set_option: staged pairs must be 0, 64, 128, 256 or 512");
+        }
+        ctx->opt_trace_top = int(value);
+        return SPK_OK;
     case SPK_OPT_BUILD_MAX_LEAF:
         if (value < 1 || value > 15)
         {
@@ -480,6 +531,24 @@ int spk_cuda_set_stream(SpkContext *ctx, void *cuda_stream)
 
 namespace spk
 {
+// The run of pair slots the ray-batch kernel may stage in shared memory (SPK_OPT_TRACE_SMEM_TOP): the TLAS when the scene
+// has one with inner nodes (every ray starts there), else the top levels of the first mesh's BLAS.
+void choose_top_region(SpkContext *ctx)
+{
+    ctx->scene.top_base = 0;
+    ctx->scene.top_count = 0;
+    if (ctx->tlas_tree.num_pairs > 0)
+    {
+        ctx->scene.top_base = ctx->tlas_tree.pair_base;
+        ctx->scene.top_count = ctx->tlas_tree.num_pairs;
+    }
+    else if (!ctx->mesh_trees.empty() && ctx->mesh_trees[0].num_pairs > 0)
+    {
+        ctx->scene.top_base = ctx->mesh_trees[0].pair_base;
+        ctx->scene.top_count = ctx->mesh_trees[0].num_pairs;
+    }
+}
+
 // TLAS::Build on the device: world boxes of the primitives (AABB::TransformTo of the mesh bounds, SceneRenderProxy.cpp:41-47;
 // centre +- radius for spheres) -> LBVH with one primitive per leaf -> instances in the order of the sorted leaves.
 int rebuild_tlas_on_device(SpkContext *ctx, const SpkPrimitiveDesc *prims, uint32_t n)
@@ -827,7 +896,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         const SpkMeshDesc &md = s->meshes[it.mesh];
         if (it.begin == it.end)
         {
-            flatten_pairs(md.blas, it.pair_base, it.tri_base, pairs + size_t(it.pair_base) * 16);
+            flatten_pairs(md.blas, it.pair_base, it.tri_base, pairs + size_t(it.pair_base) * 16, ctx->opt_trace_top > 0);
             ctx->mesh_root_word[it.mesh] = root_word(md.blas, it.pair_base, it.tri_base);
             ctx->mesh_trees[it.mesh].root_word = ctx->mesh_root_word[it.mesh];
             return;
@@ -966,6 +1035,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     ctx->scene.tlas_root = tlas_root_keep;
     ctx->scene.cull_extent = s->world_extent > 0.f ? s->world_extent : 1.f;
     ctx->scene.sky = sky;
+    choose_top_region(ctx);
     ctx->has_scene = true;
     ctx->tracer_choice = -1; // measured again for the new scene (spk_cuda_choose_tracer)
     return SPK_OK;
@@ -1013,6 +1083,7 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
         {
             ctx->scene.cull_extent = extent;
         }
+        choose_top_region(ctx);
         return SPK_OK;
     }
     int rc = validate_bvh(*tlas, num_primitives, "spk_cuda_update_instances: malformed TLAS");
@@ -1054,6 +1125,7 @@ int spk_cuda_update_instances(SpkContext *ctx, const SpkPrimitiveDesc *primitive
     ctx->tlas_tree.root_word = ctx->scene.tlas_root;
     ctx->tlas_tree.num_pairs = tlas_pairs;
     ctx->tlas_tree.device_built = false;
+    choose_top_region(ctx);
     // the t-culling slack is sized from the world extent (spk_traverse.cuh): primitives may have moved outside the
     // bounds of the upload, so take it again from the rebuilt TLAS root (= the world AABB)
     const HostNode root = read_node(*tlas, 0);

@@ -8,8 +8,8 @@
  *   boxes + centroids  -> 30-bit Morton codes on the centroid bounds -> radix sort (cub::DeviceRadixSort, the one library
  *   call: a plain key-value sort) -> Karras' binary radix tree over the sorted codes (ties broken by position) -> bottom-up
  *   AABB fit -> subtrees of <= max_leaf primitives collapse into leaves (sorted order makes every subtree a contiguous run)
- *   -> surviving inner nodes numbered level by level (a second, 6-bit sort by depth: parents precede children, the top of the
- *   tree is one contiguous run) -> sibling pairs and leaf-ordered triangle records written in place.
+ *   -> surviving inner nodes numbered in depth-first preorder (a prefix sum + one walk to the root per node: parents precede
+ *   children, a left child's pair is the next 64 bytes) -> sibling pairs and leaf-ordered triangle records written in place.
  *
  * The same kernels build the TLAS from the instances' world boxes (max_leaf 1). spk_cuda_download_bvh hands any tree on the
  * device back in the bvh::v2 node layout + prim_ids, so the oracle traverses the SAME topology (tests/test_build_gpu.py:
@@ -22,6 +22,7 @@
 
 #include <cfloat>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cstring>
 
 namespace spk
@@ -275,46 +276,58 @@ __global__ void fit_bounds_kernel(const float *__restrict__ boxes, const uint32_
     }
 }
 
-// which radix-tree nodes survive as inner nodes (more than max_leaf primitives below them), and their depth: the sort key
-// that numbers the pair slots level by level, so a parent always precedes its children (the bvh::v2 layout the host
-// builder and the reference produce, and what validate_bvh checks) and the top of the tree is one contiguous run
-__global__ void mark_inner_kernel(const uint32_t *__restrict__ first, const uint32_t *__restrict__ last,
-                                  const uint32_t *__restrict__ parent, int n, uint32_t max_leaf, uint32_t *__restrict__ inner,
-                                  uint32_t *__restrict__ key, uint32_t *__restrict__ node, uint32_t *__restrict__ stats)
+// which radix-tree nodes survive as inner nodes (more than max_leaf primitives below them)
+__global__ void mark_inner_kernel(const uint32_t *__restrict__ first, const uint32_t *__restrict__ last, int n,
+                                  uint32_t max_leaf, uint32_t *__restrict__ inner)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool is_inner = false;
-    uint32_t depth = 0;
     if (i < n - 1)
     {
-        is_inner = (last[i] - first[i] + 1u) > max_leaf;
-        for (uint32_t p = parent[i]; p != 0xFFFFFFFFu; p = parent[p])
+        inner[i] = (last[i] - first[i] + 1u) > max_leaf ? 1u : 0u;
+    }
+}
+
+// Pair slots in DEPTH-FIRST PREORDER: a parent precedes its children (the bvh::v2 layout of the host builder, and what
+// validate_bvh checks) and the left child's pair is the next 64 bytes, i.e. often the other half of the 128-byte line
+// the parent's fetch just brought in. The internal nodes of a subtree are a contiguous run of indices, so with S = exclusive
+// prefix sum of the `inner` flags the number of surviving inner nodes in a subtree is a difference of two entries of S, and
+// preorder(node) = sum over the path to the root of (1 + inner nodes of the left sibling subtree when
+// the path goes right; a left child [f, g] has index g and owns the internal indices f+1 .. g). A level-by-level numbering
+// (sort by depth) was measured too: the same speed on incoherent rays (soup-1M 1238 vs 1236 Mrays/s), so the order that
+// matches the host builder's was kept.
+__global__ void preorder_slots_kernel(const uint32_t *__restrict__ left, const uint32_t *__restrict__ parent,
+                                      const uint32_t *__restrict__ first, const uint32_t *__restrict__ last,
+                                      const uint32_t *__restrict__ inner, const uint32_t *__restrict__ prefix, int n,
+                                      uint32_t *__restrict__ slot, uint32_t *__restrict__ stats)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool is_inner = i < n - 1 && inner[i];
+    uint32_t depth = 0;
+    if (is_inner)
+    {
+        uint32_t pre = 0, c = (uint32_t)i;
+        for (uint32_t p = parent[c]; p != 0xFFFFFFFFu; c = p, p = parent[p])
         {
+            pre += 1u;
+            const uint32_t l = left[p];
+            if (l != c && !(l & kLeafBit))
+            {
+                // surviving inner nodes of the left sibling's subtree: a LEFT child sits at the last position of its range
+                // [f, g], and the internal nodes below it are f+1 .. g
+                pre += prefix[last[l] + 1u] - prefix[first[l] + 1u];
+            }
             depth++;
         }
-        inner[i] = is_inner ? 1u : 0u;
-        key[i] = is_inner ? min(depth, 62u) : 63u;
-        node[i] = (uint32_t)i;
+        slot[i] = pre;
     }
-    const uint32_t vote = __ballot_sync(0xffffffffu, is_inner);
     uint32_t deepest = is_inner ? depth + 1u : 0u; // its children sit one level below
     for (int d = 16; d; d >>= 1)
     {
         deepest = max(deepest, __shfl_xor_sync(0xffffffffu, deepest, d));
     }
-    if ((threadIdx.x & 31) == 0 && vote)
+    if ((threadIdx.x & 31) == 0 && deepest)
     {
-        atomicAdd(&stats[1], (uint32_t)__popc(vote));
         atomicMax(&stats[0], deepest);
-    }
-}
-
-__global__ void assign_slots_kernel(const uint32_t *__restrict__ order, uint32_t count, uint32_t *__restrict__ slot)
-{
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k < count)
-    {
-        slot[order[k]] = k;
     }
 }
 
@@ -429,8 +442,7 @@ int device_build_lbvh(SpkContext *ctx, const float *d_vertices, const uint32_t *
     size_t sort_bytes = 0, scan_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
                                     (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 30, s);
-    cub::DeviceRadixSort::SortPairs(nullptr, scan_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
-                                    (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 6, s);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, s);
     size_t need = 0;
     auto take = [&](size_t bytes) {
         const size_t at = need;
@@ -522,15 +534,16 @@ int device_build_lbvh(SpkContext *ctx, const float *d_vertices, const uint32_t *
         radix_tree_kernel<<<iblocks, T, 0, s>>>(b.codes_sorted, (int)n, b.left, b.right, b.parent, b.leaf_parent, b.first, b.last);
         fit_bounds_kernel<<<blocks, T, 0, s>>>(boxes, b.ids_sorted, (int)n, b.left, b.right, b.parent, b.leaf_parent,
                                                b.node_boxes, b.visits);
-        // (codes, ids and the fit counters are free again: sort keys, node indices and the level order reuse them)
-        mark_inner_kernel<<<iblocks, T, 0, s>>>(b.first, b.last, b.parent, (int)n, max_leaf, b.inner, b.codes, b.ids, b.stats);
+        mark_inner_kernel<<<iblocks, T, 0, s>>>(b.first, b.last, (int)n, max_leaf, b.inner);
         SPK_CUDA_TRY(cudaGetLastError());
+        // (the Morton codes are not needed any more: their buffer takes the prefix sum, one entry more than inner nodes)
+        SPK_CUDA_TRY(cudaMemsetAsync(b.inner + (n - 1), 0, 4, s));
         tmp = std::max(sort_bytes, scan_bytes);
-        SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairs(cub_tmp, tmp, b.codes, b.codes_sorted, b.ids, b.visits, (int)(n - 1), 0, 6, s));
-        SPK_CUDA_TRY(cudaMemcpyAsync(stats_host, b.stats, 16, cudaMemcpyDeviceToHost, s));
+        SPK_CUDA_TRY(cub::DeviceScan::ExclusiveSum(cub_tmp, tmp, b.inner, b.codes, (int)n, s));
+        preorder_slots_kernel<<<iblocks, T, 0, s>>>(b.left, b.parent, b.first, b.last, b.inner, b.codes, (int)n, b.slot, b.stats);
+        uint32_t inner_count = 0;
+        SPK_CUDA_TRY(cudaMemcpyAsync(&inner_count, b.codes + (n - 1), 4, cudaMemcpyDeviceToHost, s));
         SPK_CUDA_TRY(cudaStreamSynchronize(s));
-        const uint32_t inner_count = stats_host[1];
-        assign_slots_kernel<<<(inner_count + T - 1) / T, T, 0, s>>>(b.visits, inner_count, b.slot);
         emit_pairs_kernel<<<iblocks, T, 0, s>>>(boxes, b.ids_sorted, (int)n, b.left, b.right, b.parent, b.first, b.last,
                                                 b.node_boxes, b.inner, b.slot, pair_base, leaf_base, d_pairs, b.stats);
         SPK_CUDA_TRY(cudaGetLastError());

@@ -86,6 +86,7 @@ struct SpkContext
     uint32_t opt_wf_slots = 1u << 24; // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
     uint32_t opt_wf_chunk = 8;
     int opt_vote = 6;
+    int opt_trace_top = 0; // pairs of the hottest tree's top staged in shared memory by the ray-batch kernel (0 = off)
     int opt_carveout = -2;
     bool opt_verbose = false;
     int tracer_choice = -1; // -1 not measured for this scene, 0 megakernel, 1 wavefront (spk_cuda_choose_tracer)

@@ -100,6 +100,8 @@ struct DScene
     uint32_t tlas_root;         // index word of the TLAS root (absolute)
     uint32_t num_instances;     // 0 => empty scene
     float cull_extent;          // world extent used for the t-culling slack
+    uint32_t top_base;          // first pair slot of the run a kernel may stage in shared memory (the hottest tree's top)
+    uint32_t top_count;         // pairs in that run (level-ordered: any prefix is the top of the tree)
     uint32_t pad;
     DSky sky;
 };

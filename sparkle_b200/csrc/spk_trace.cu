@@ -59,13 +59,19 @@ __global__ void __launch_bounds__(kTraceThreads)
 // ---- persistent, warp-converged form (spk_traverse_warp.cuh): the default for ray batches ----
 constexpr int kPersistWarps = 4;
 
-template <bool CULL, bool COUNT, int VOTE>
+template <bool CULL, bool COUNT, int VOTE, bool TOP = false>
 __global__ void __launch_bounds__(kPersistWarps * 32)
     trace_persistent_kernel(const DScene sc, const float4 *__restrict__ rays, unsigned long long n,
                             float *__restrict__ hits, unsigned long long *__restrict__ counters,
-                            unsigned long long *__restrict__ next_ray)
+                            unsigned long long *__restrict__ next_ray, uint32_t top_pairs)
 {
     __shared__ uint32_t s_lane_words[kPersistWarps * kLaneSmemWords * 32];
+    extern __shared__ __align__(16) unsigned char s_top_bytes[]; // TOP: top_pairs x 64 bytes
+    TopOfTree top{reinterpret_cast<const float4 *>(s_top_bytes), sc.top_base, TOP ? min(sc.top_count, top_pairs) : 0u};
+    if (TOP)
+    {
+        stage_top_of_tree(sc.pairs, reinterpret_cast<float4 *>(s_top_bytes), top.base, top.count);
+    }
     TraceCounters cnt{0, 0, 0, 0};
     auto write_hit = [&](unsigned long long id, const Hit &best) {
         float *o = hits + 5 * id;
@@ -76,7 +82,7 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
         o[3] = __uint_as_float(prim);
         o[4] = __uint_as_float(best.face);
     };
-    warp_trace_loop<CULL, COUNT, 16, VOTE>(
+    warp_trace_loop<CULL, COUNT, 16, VOTE, TOP>(
         sc, n, next_ray, s_lane_words, cnt,
         [&](unsigned long long id, V3 &o, V3 &d) {
             if (sc.num_instances == 0)
@@ -90,7 +96,7 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
             d = mk(rd.x, rd.y, rd.z);
             return true;
         },
-        write_hit);
+        write_hit, top);
     if (COUNT)
     {
         const unsigned lane = threadIdx.x & 31u;
@@ -108,25 +114,35 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
 }
 } // namespace
 
-template <bool CULL, bool COUNT, int VOTE>
+template <bool CULL, bool COUNT, int VOTE, bool TOP = false>
 static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, float *hits)
 {
-    auto kernel = trace_persistent_kernel<CULL, COUNT, VOTE>;
+    auto kernel = trace_persistent_kernel<CULL, COUNT, VOTE, TOP>;
+    const uint32_t top_pairs = TOP ? uint32_t(ctx->opt_trace_top) : 0u;
+    const size_t dynamic = size_t(top_pairs) * 64;
     static int blocks_per_sm = 0, sms = 0;
-    if (blocks_per_sm == 0)
+    static size_t measured_for = ~size_t(0);
+    if (measured_for != dynamic)
     {
-        SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, 0));
+        if (dynamic > 48 * 1024)
+        {
+            SPK_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dynamic));
+        }
+        const size_t per_cta = sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32 + dynamic;
+        // ask for the carve-out that holds 8 CTAs (the register limit) if the array allows it, then see what fits
+        SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, per_cta, 8, ctx->opt_carveout));
+        SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, dynamic));
         SPK_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
         blocks_per_sm = blocks_per_sm < 1 ? 1 : blocks_per_sm;
-        SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32, blocks_per_sm,
-                                                 ctx->opt_carveout));
+        SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, per_cta, blocks_per_sm, ctx->opt_carveout));
+        measured_for = dynamic;
     }
     uint64_t want = (n + kPersistWarps * 32 - 1) / (kPersistWarps * 32);
     uint64_t resident = uint64_t(blocks_per_sm) * sms; // one wave of persistent CTAs: a multiple of the SM count
     unsigned grid = unsigned(want < resident ? want : resident);
     unsigned long long *next_ray = ctx->d_counters + 7;
     SPK_CUDA_TRY(cudaMemsetAsync(next_ray, 0, sizeof(unsigned long long), ctx->stream));
-    kernel<<<grid, kPersistWarps * 32, 0, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters, next_ray);
+    kernel<<<grid, kPersistWarps * 32, dynamic, ctx->stream>>>(ctx->scene, rays, n, hits, ctx->d_counters, next_ray, top_pairs);
     return SPK_OK;
 }
 
@@ -166,6 +182,11 @@ int launch_trace_closest(SpkContext *ctx, const void *d_rays, uint64_t n, void *
         rc = launch_persistent<true, true, 8>(ctx, rays, n, hits);
     else
     {
+        if (ctx->opt_trace_top > 0)
+        {
+            rc = launch_persistent<true, false, 6, true>(ctx, rays, n, hits);
+        }
+        else
         switch (ctx->opt_vote)
         {
         case 4: rc = launch_persistent<true, false, 4>(ctx, rays, n, hits); break;

@@ -125,15 +125,48 @@ __device__ __forceinline__ bool lane_pop(LaneState &s, LaneStack &stack)
     }
 }
 
-// one bvh::v2 inner step (the loop body of trace_closest); returns false when the ray is finished
-template <bool CULL, bool COUNT>
-__device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs, LaneState &s, LaneStack &stack,
-                                                TraceCounters &cnt)
+// The top of the hottest tree staged in shared memory (north_star: "the top levels staged in shared memory"): `count` pairs
+// starting at pair slot `base`, 64 bytes each. The four 16-byte quarters of pair p are stored rotated by (p >> 1) & 3, so
+// that eight lanes reading the same quarter of eight different pairs touch eight different bank groups.
+struct TopOfTree
 {
-    const float4 *p = pairs + size_t(s.top >> 4) * 4;
+    const float4 *sm;
+    uint32_t base, count;
+};
+
+__device__ __forceinline__ void stage_top_of_tree(const float4 *__restrict__ pairs, float4 *sm, uint32_t base, uint32_t count)
+{
+    for (uint32_t k = threadIdx.x; k < count * 4u; k += blockDim.x)
+    {
+        const uint32_t p = k >> 2, q = k & 3u;
+        sm[p * 4u + (q ^ ((p >> 1) & 3u))] = __ldg(pairs + size_t(base + p) * 4 + q);
+    }
+    __syncthreads();
+}
+
+// one bvh::v2 inner step (the loop body of trace_closest); returns false when the ray is finished
+template <bool CULL, bool COUNT, bool TOP = false>
+__device__ __forceinline__ bool lane_inner_step(const float4 *__restrict__ pairs, LaneState &s, LaneStack &stack,
+                                                TraceCounters &cnt, const TopOfTree &top = TopOfTree{nullptr, 0, 0})
+{
+    const uint32_t slot = s.top >> 4;
     float4 l0, l1, r0, r1;
-    ldg256(p, l0, l1);
-    ldg256(p + 2, r0, r1);
+    const uint32_t rel = slot - top.base;
+    if (TOP && rel < top.count)
+    {
+        const float4 *q = top.sm + rel * 4u;
+        const uint32_t rot = (rel >> 1) & 3u;
+        l0 = q[0u ^ rot];
+        l1 = q[1u ^ rot];
+        r0 = q[2u ^ rot];
+        r1 = q[3u ^ rot];
+    }
+    else
+    {
+        const float4 *p = pairs + size_t(slot) * 4;
+        ldg256(p, l0, l1);
+        ldg256(p + 2, r0, r1);
+    }
     if (COUNT)
     {
         cnt.node_visits++;
@@ -244,9 +277,10 @@ __device__ __forceinline__ bool lane_tlas_step(const DScene &sc, LaneState &s, L
  * id and returns false to skip it, store(id, best) writes its closest hit. REFILL: idle lanes wait until this many are
  * idle (or nothing else is left to do) before one lane fetches a block of ray ids with a single atomic.
  */
-template <bool CULL, bool COUNT, int REFILL, int VOTE, typename Fetch, typename Store>
+template <bool CULL, bool COUNT, int REFILL, int VOTE, bool TOP = false, typename Fetch, typename Store>
 __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long long n, unsigned long long *cursor,
-                                                uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch, Store &&store)
+                                                uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch, Store &&store,
+                                                const TopOfTree &top = TopOfTree{nullptr, 0, 0})
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -317,7 +351,7 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
         }
         else if (is_inner)
         {
-            active = lane_inner_step<CULL, COUNT>(pairs, s, stack, cnt);
+            active = lane_inner_step<CULL, COUNT, TOP>(pairs, s, stack, cnt, top);
         }
         // lanes whose stack ran empty: the ray is finished
         if (!active && ray_id != ~0ull)
