@@ -486,7 +486,15 @@ bool GetView(Model &m, int accessor_id, View &out)
     const std::string type = acc.Str("type");
     out.width = type == "SCALAR" ? 1 : type == "VEC2" ? 2 : type == "VEC3" ? 3 : type == "VEC4" ? 4 : 0;
     out.component = acc.Int("componentType", 0);
-    out.count = static_cast<size_t>(acc.Num("count", 0));
+    // counts, offsets and strides come from JSON doubles: range-check them BEFORE any cast or product (a negative or huge
+    // value is undefined behaviour on the cast, and a wrapped product would pass the bounds check below)
+    const double max_bytes = 4294967296.0 * 16.0; // far above any buffer this reader loads
+    const double count_d = acc.Num("count", 0);
+    if (!(count_d >= 0.0 && count_d <= max_bytes))
+    {
+        return Fail("accessor count out of range");
+    }
+    out.count = static_cast<size_t>(count_d);
     const int cb = ComponentBytes(out.component);
     const auto &views = m.root.Arr("bufferViews");
     const int bv = acc.Int("bufferView", -1);
@@ -509,15 +517,23 @@ bool GetView(Model &m, int accessor_id, View &out)
         }
         m.buffer_loaded[size_t(buf)] = true;
     }
-    const size_t offset = static_cast<size_t>(view.Num("byteOffset", 0)) + static_cast<size_t>(acc.Num("byteOffset", 0));
+    const double view_off = view.Num("byteOffset", 0), acc_off = acc.Num("byteOffset", 0), stride_d = view.Num("byteStride", 0);
+    const auto &bytes = m.buffers[size_t(buf)];
+    const double size_d = double(bytes.size());
+    if (!(view_off >= 0.0 && view_off <= size_d && acc_off >= 0.0 && acc_off <= size_d && stride_d >= 0.0 && stride_d <= size_d))
+    {
+        return Fail("accessor offset or stride out of range");
+    }
+    const size_t offset = static_cast<size_t>(view_off) + static_cast<size_t>(acc_off);
     const size_t elem = size_t(cb) * size_t(out.width);
-    out.stride = static_cast<size_t>(view.Num("byteStride", 0));
+    out.stride = static_cast<size_t>(stride_d);
     if (out.stride == 0)
     {
         out.stride = elem; // Accessor::ByteStride: tightly packed
     }
-    const auto &bytes = m.buffers[size_t(buf)];
-    if (out.count && offset + (out.count - 1) * out.stride + elem > bytes.size())
+    // every term is <= bytes.size() and the count is bounded above, so the 128-bit product cannot wrap
+    const unsigned __int128 last = (unsigned __int128)offset + (unsigned __int128)(out.count ? out.count - 1 : 0) * out.stride + elem;
+    if (out.count && last > (unsigned __int128)bytes.size())
     {
         return Fail("accessor runs past the end of its buffer");
     }
