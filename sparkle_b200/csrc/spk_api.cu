@@ -71,9 +71,11 @@ uint32_t read_prim_id(const SpkBvhDesc &d, uint32_t k)
 // structural checks the reference never makes (a malformed tree would overflow its SmallStack<Index,32>)
 // host-side flattening of a 1M-triangle scene on one thread was 110 ms of every end-to-end step: work items are spread
 // over up to 8 host threads (errors are reported by index, the message is set by the caller's thread)
-template <typename Fn> void parallel_for(size_t n, Fn &&fn)
+// (`worth_it` false: a small scene - spawning threads costs more than the work, and with one process per GPU eight of them
+// would fight over the same host cores: TestScene's upload went 1.2 -> ms at 8 ranks)
+template <typename Fn> void parallel_for(size_t n, Fn &&fn, bool worth_it = true)
 {
-    unsigned workers = std::min<size_t>(std::min(8u, std::max(1u, std::thread::hardware_concurrency())), n);
+    unsigned workers = worth_it ? std::min<size_t>(std::min(8u, std::max(1u, std::thread::hardware_concurrency())), n) : 1u;
     if (workers <= 1)
     {
         for (size_t i = 0; i < n; i++)
@@ -644,6 +646,12 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     }
     uint64_t total_pairs = 0, total_tris = 0;
     std::vector<int> mesh_status(s->num_meshes, 0); // 0 ok, 1 missing arrays, 2 index out of range, 3 malformed BLAS
+    uint64_t faces_in = 0;
+    for (uint32_t m = 0; m < s->num_meshes; m++)
+    {
+        faces_in += s->meshes[m].num_faces;
+    }
+    const bool big_scene = faces_in > 100000u; // host threads pay off from ~5 MB of tables
     parallel_for(s->num_meshes, [&](size_t m) {
         const SpkMeshDesc &md = s->meshes[m];
         if (!md.vertices || !md.normals || !md.tangents || !md.indices || md.num_faces == 0 || md.num_vertices == 0)
@@ -667,7 +675,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         {
             mesh_status[m] = 3;
         }
-    });
+    }, big_scene);
     for (uint32_t m = 0; m < s->num_meshes; m++)
     {
         if (mesh_status[m] != 0)
@@ -919,7 +927,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
             o[7] = 0.f;
             o[11] = 0.f;
         }
-    });
+    }, big_scene || plan.used > (size_t(8) << 20));
     ctx->num_blas_pairs = pair_base;
     ctx->tlas_pair_base = pair_base;
 
