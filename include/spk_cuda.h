@@ -331,7 +331,7 @@ int spk_cuda_group_destroy(SpkGroup *group);
 
 /* Tuning knobs, explicit (nothing in the library reads the environment). Defaults are the measured choices. */
 typedef enum SpkOption {
-    SPK_OPT_MEGAKERNEL_FORM = 0, /* 0 = measured choice (spk_cuda_choose_tracer; 1162 until measured). Forms: 1162 / 1084 /
+    SPK_OPT_MEGAKERNEL_FORM = 0, /* 0 = measured choice (spk_cuda_choose_tracer; 1084 until measured). Forms: 1162 / 1084 /
                                     1083 sorted megakernel, 16 warps x 2 / 8 x 4 / 8 x 3 CTAs per SM, pixels owned by a
                                     CTA; 3162 / 3084 the same with the sort kept in pixel order inside a class; 2162 /
                                     2084 persistent pixel-pulling grid; 831 / 830 / 1621 / 461 phased kernel; 1 = plain
@@ -343,6 +343,8 @@ typedef enum SpkOption {
                                     default, -2 (default) the smallest that holds the resident CTAs */
     SPK_OPT_VERBOSE = 5,         /* 1: spk_cuda_choose_tracer prints its timings to stderr */
     SPK_OPT_BUILD_MAX_LEAF = 6,  /* triangles per leaf of device-built BLAS (1..15, default 4) */
+    SPK_OPT_COST_ORDERED_STRIPS = 8, /* sorted megakernel: launch the strips of tiles in the order of their cost in the
+                                    previous launch of the same view, longest first (default 1) */
     SPK_OPT_TRACE_SMEM_TOP = 7   /* ray-batch kernel: pairs of the hottest tree's top levels (the TLAS, else the first BLAS)
                                     staged in shared memory: 0 (default, measured), 64, 128, 256, 512 */
 } SpkOption;

@@ -75,12 +75,19 @@ struct SpkContext
     };
     std::vector<TreeInfo> mesh_trees;
     TreeInfo tlas_tree;
+    // sorted megakernel: strips of tiles launched in the order of their cost in the previous launch of the view
+    uint32_t *d_strip = nullptr;
+    uint32_t strip_capacity = 0, strip_order_count = 0;
+    size_t strip_tmp_bytes = 0;
+    int strip_order_form = 0;
+    bool strip_order_valid = false;
+    bool opt_cost_order = true;
     void *d_group_block = nullptr; // multi-GPU: flags + the root's gathered output, visible to peers (spk_group.cu)
 
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
     void *wf_block = nullptr;
     uint32_t wf_slots = 0;
-    int mega_variant = 1162; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
+    int mega_variant = 1084; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
     // explicit options (spk_cuda_set_option); nothing is read from the environment
     int opt_mega_form = 0;           // 0: use mega_variant
     uint32_t opt_wf_slots = 1u << 24; // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)

@@ -124,7 +124,11 @@ __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y -
 __device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+#ifdef SPK_NOINLINE_DIV3
+static __device__ __noinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+#else
 __device__ __forceinline__ V3 operator/(V3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+#endif
 __device__ __forceinline__ V3 cmul(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 __device__ __forceinline__ float sqnorm(V3 a) { return a.x * a.x + (a.y * a.y + a.z * a.z); }
@@ -143,7 +147,17 @@ __device__ __forceinline__ float div_by_norm(float a, float n, bool n_pos)
     float q = (zero ? n : a) / n;
     return zero ? a : q;
 }
+// ONE out-of-line copy instead of ~15 inlined ones (each a square root and three IEEE divisions with their slow-path
+// stubs, ~60 instructions): the sorted megakernel shrank from 4880 to 4144 SASS instructions (76 -> 65 KB), and with it the
+// instruction-cache misses that made small CTAs lose: TestScene 1080p x 32 spp 19.04 -> 18.04 ms with 16 warps x 2 CTAs
+// and 21.69 -> 17.91 ms with 8 warps x 4 (B200; room 122.0 -> 120.8). Going further (rng_seed, make_slab_ray, V3 / float
+// out of line as well) measured 0.5-4 % SLOWER each: those have one or two call sites and the call costs more than the
+// bytes. -DSPK_INLINE_NORM restores the inlined form for A/B builds.
+#ifndef SPK_INLINE_NORM
+static __device__ __noinline__ V3 normalized(V3 a)
+#else
 __device__ __forceinline__ V3 normalized(V3 a)
+#endif
 {
     float sq = sqnorm(a);
     float n = sq > 0.f ? sqrtf(sq) : sq;

@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cub/device/device_radix_sort.cuh>
 #include "spk_shade.cuh"
 #include "spk_traverse.cuh"
 
@@ -420,9 +421,16 @@ template <int WARPS> constexpr size_t sorted_smem_bytes()
 template <bool CULL, bool COUNT, int WARPS, int MINB, int MODE>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
     render_sorted_kernel(const DScene sc, const DCamera cam, const RenderArgs a, float4 *__restrict__ accum,
-                         unsigned long long *__restrict__ counters)
+                         unsigned long long *__restrict__ counters, const uint32_t *__restrict__ cta_order,
+                         uint32_t *__restrict__ cta_cost)
 {
     constexpr bool PULL = MODE == 1, STABLE = MODE == 2;
+    // Owner forms: which strip of tiles this CTA renders. The hardware hands CTAs out in blockIdx order; cta_order (when
+    // given) lists the strips by DECREASING cost of the previous launch of the same view, so the long strips (glass,
+    // deep meshes) start first and the last wave is made of short ones (longest-processing-time-first: the tail of the
+    // grid was ~6 % of the launch). cta_cost receives this launch's cycles per strip for the next one.
+    const long long t_start = clock64();
+    const uint32_t strip = (!PULL && cta_order) ? cta_order[blockIdx.x] : blockIdx.x;
     constexpr int T = WARPS * 32;
     __shared__ uint8_t s_key[STABLE ? T : 1]; // STABLE: the shading class of every column's parked segment, 0xFF = no path
     extern __shared__ __align__(16) unsigned char s_dynamic[]; // sorted_smem_bytes<WARPS>()
@@ -437,7 +445,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
     constexpr uint32_t kSampleShift = PULL ? 15u : 8u; // packed word: sample above, (pixel_hi,) bounce below
     // column c of the CTA <-> pixel: a warp-sized run of columns is one 8x4 tile
     auto pixel_of = [&](uint32_t c, uint32_t &pi, uint32_t &pj) {
-        const uint32_t w = blockIdx.x * WARPS + (c >> 5), l = c & 31u;
+        const uint32_t w = strip * WARPS + (c >> 5), l = c & 31u;
         pi = (w % tiles_x) * kTileW + (l & (kTileW - 1));
         pj = (w / tiles_x) * kTileH + (l / kTileW);
     };
@@ -817,6 +825,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
         const float *own = s_state + tid;
         accum[size_t(j) * a.width + i] = make_float4(own[19 * T], own[20 * T], own[21 * T], own[22 * T]);
     }
+    if (!PULL && cta_cost && tid == 0)
+    {
+        cta_cost[strip] = (uint32_t)min((clock64() - t_start) >> 6, 0xFFFFFFFFll);
+    }
     uint32_t total = __reduce_add_sync(0xffffffffu, rays);
     uint32_t pixels = PULL ? __reduce_add_sync(0xffffffffu, pixels_done) : __popc(__ballot_sync(0xffffffffu, in_image));
     if (lane == 0 && (pixels || total))
@@ -965,6 +977,55 @@ int copy_to_host(SpkContext *ctx, void *host_out, const void *d_src, size_t byte
     return SPK_OK;
 }
 
+// ---- cost-ordered strips (owner forms of the sorted megakernel) ----
+// d_strip: [cost | cost_sorted | iota | order] of `capacity` entries each + cub scratch. The order belongs to one (strip
+// count, form). It is only a schedule - any permutation renders the same image bit for bit - so it is KEPT across camera
+// moves and scene uploads: a progressive renderer draws nearly the same view again and again, and after a cut the stale
+// order is merely no better than any other. Measured (B200, 1080p): TestScene 256 spp 138.97 -> 130.50 ms, room 943.5 ->
+// 933.3 ms (tools/r2_cost_order_ab.py); SPK_OPT_COST_ORDERED_STRIPS = 0 turns it off.
+int strip_order_prepare(SpkContext *ctx, uint32_t strips, int form, const uint32_t **order, uint32_t **cost)
+{
+    if (ctx->strip_capacity < strips)
+    {
+        cudaFree(ctx->d_strip);
+        ctx->d_strip = nullptr;
+        ctx->strip_capacity = 0;
+        size_t tmp = 0;
+        cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+                                                  (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)strips, 0, 32, ctx->stream);
+        ctx->strip_tmp_bytes = tmp;
+        SPK_CUDA_TRY(cudaMalloc(&ctx->d_strip, size_t(strips) * 16 + tmp + 256));
+        ctx->strip_capacity = strips;
+        std::vector<uint32_t> iota(strips);
+        for (uint32_t k = 0; k < strips; k++)
+        {
+            iota[k] = k;
+        }
+        SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_strip + 2 * size_t(strips), iota.data(), size_t(strips) * 4, cudaMemcpyHostToDevice,
+                                     ctx->stream));
+        SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        ctx->strip_order_valid = false;
+    }
+    const size_t cap = ctx->strip_capacity;
+    *cost = ctx->d_strip;
+    *order = (ctx->strip_order_valid && ctx->strip_order_count == strips && ctx->strip_order_form == form) ? ctx->d_strip + 3 * cap
+                                                                                                          : nullptr;
+    return SPK_OK;
+}
+
+int strip_order_update(SpkContext *ctx, uint32_t strips, int form)
+{
+    const size_t cap = ctx->strip_capacity;
+    size_t tmp = ctx->strip_tmp_bytes;
+    SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(ctx->d_strip + 4 * cap, tmp, ctx->d_strip, ctx->d_strip + cap,
+                                                           ctx->d_strip + 2 * cap, ctx->d_strip + 3 * cap, (int)strips, 0, 32,
+                                                           ctx->stream));
+    ctx->strip_order_valid = true;
+    ctx->strip_order_count = strips;
+    ctx->strip_order_form = form;
+    return SPK_OK;
+}
+
 int launch_render(SpkContext *ctx, const SpkRenderParams *p)
 {
     RenderArgs a;
@@ -1002,7 +1063,7 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
     const DScene &scene = ctx->scene;
     const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
     // the form of the megakernel: SPK_OPT_MEGAKERNEL_FORM forces one (A/B runs), otherwise the one
-    // spk_cuda_choose_tracer measured fastest on this scene (1162 until measured)
+    // spk_cuda_choose_tracer measured fastest on this scene (1084 until measured)
     int phased = ctx->opt_mega_form > 0 ? ctx->opt_mega_form : ctx->mega_variant;
     const uint32_t total_px = tiles * 32u;
     if (phased >= 2000 && phased < 3000 && (a.sample_count >= (1u << 17) || total_px >= (1u << 23)))
@@ -1023,12 +1084,26 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
             // the pixel counter of the pulling form (counters[7]) starts every launch at zero
             SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), ctx->stream));
         }
+        // strips in the order of their cost in the previous launch of this view (owner forms, launches of >= 8 spp)
+        const uint32_t strip_warps = uint32_t((phased % 1000) / 10);
+        const uint32_t strips = (tiles + strip_warps - 1) / strip_warps;
+        const uint32_t *strip_order = nullptr;
+        uint32_t *strip_cost = nullptr;
+        const bool cost_ordered = ctx->opt_cost_order && (phased < 2000 || phased >= 3000) && a.sample_count >= 8u && strips >= 64u;
+        if (cost_ordered)
+        {
+            int rc1 = strip_order_prepare(ctx, strips, phased, &strip_order, &strip_cost);
+            if (rc1 != SPK_OK)
+            {
+                return rc1;
+            }
+        }
         // form = 1000 + warps*10 + CTAs/SM: pixels owned by the CTA, one CTA per 16 tiles; 2000 + ...: persistent grid
 #define SPK_SORTED_LAUNCH(W, B, MODE, C, N)                                                                            \
     render_sorted_kernel<C, N, W, B, MODE><<<(MODE == 1) ? std::min<uint32_t>((tiles + W - 1) / W, uint32_t(sms) * B)  \
                                                     : (tiles + W - 1) / W,                                             \
                                              W * 32, sorted_smem_bytes<W>(), ctx->stream>>>(                           \
-        scene, ctx->camera, a, ctx->d_accum, ctx->d_counters)
+        scene, ctx->camera, a, ctx->d_accum, ctx->d_counters, strip_order, strip_cost)
 #define SPK_SORTED_CASE(W, B, MODE)                                                                                    \
     case 1000 * (MODE + 1) + W * 10 + B:                                                                               \
         SPK_CUDA_TRY((sorted_allow_smem<W, B, MODE>(ctx->opt_carveout)));                                              \
@@ -1046,8 +1121,6 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
             SPK_SORTED_CASE(8, 3, 0)
             SPK_SORTED_CASE(8, 4, 0)
             SPK_SORTED_CASE(16, 2, 0)
-            SPK_SORTED_CASE(32, 1, 0)
-            SPK_SORTED_CASE(24, 1, 0)
             SPK_SORTED_CASE(8, 4, 1)
             SPK_SORTED_CASE(16, 2, 1)
             SPK_SORTED_CASE(8, 4, 2)
@@ -1060,6 +1133,10 @@ int launch_render(SpkContext *ctx, const SpkRenderParams *p)
 #undef SPK_SORTED_LAUNCH
         SPK_CUDA_TRY(cudaGetLastError());
         ctx->stats.kernel_launches++;
+        if (cost_ordered)
+        {
+            return strip_order_update(ctx, strips, phased);
+        }
         return SPK_OK;
     }
     if (phased != 1 && !(p->flags & SPK_FLAG_SPATIAL_DENOISE))
@@ -1239,12 +1316,12 @@ int spk_cuda_choose_tracer(SpkContext *ctx, uint32_t max_bounce, uint32_t *wavef
     SPK_CUDA_TRY(cudaEventCreate(&e1));
     float ms[2] = {3.4e38f, 0.f};
     int rc = SPK_OK;
-    // candidates: the sorted megakernel with 16 warps x 2 CTAs/SM and with 8 warps x 4 CTAs/SM (pixels owned by the CTA; the
+    // candidates: the sorted megakernel with 8 warps x 4 CTAs/SM and with 16 warps x 2 CTAs/SM (pixels owned by the CTA; the
     // pixel-pulling forms 2162 / 2084 measured 8-15 % slower on TestScene and room and stay as options), then the wavefront tracer
     // (the phased kernel has not won on any scene since the sorted form keeps its path slots in shared memory; it stays
     // as the fallback for probes, zero-bounce and > 255-bounce launches). A later form replaces the incumbent only when
     // it is more than 3 % faster: short timings of near-equal forms are noise.
-    static const int kForms[3] = {1162, 1084, -1};
+    static const int kForms[3] = {1084, 1162, -1};
     int best_form = kForms[0];
     for (int which = 0; which < 3 && rc == SPK_OK; which++)
     {

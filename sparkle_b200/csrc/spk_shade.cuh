@@ -70,7 +70,11 @@ __device__ __forceinline__ uint32_t splitmix_next(unsigned long long &x)
     return (uint32_t)(z ^ (z >> 31));
 }
 
+#ifdef SPK_NOINLINE_SEED
+static __device__ __noinline__ Rng rng_seed(uint32_t seed)
+#else
 __device__ __forceinline__ Rng rng_seed(uint32_t seed)
+#endif
 {
     unsigned long long x = seed;
     Rng r;

@@ -34,7 +34,11 @@ struct SlabRay
     bool nx, ny, nz;  // octant: direction sign bits
 };
 
+#ifdef SPK_NOINLINE_SLAB
+static __device__ __noinline__ SlabRay make_slab_ray(V3 o, V3 d)
+#else
 __device__ __forceinline__ SlabRay make_slab_ray(V3 o, V3 d)
+#endif
 {
     SlabRay r;
     r.ix = safe_inverse(d.x);

@@ -15,8 +15,8 @@ ctx = CudaContext(w, h)
 ctx.upload_scene(sb.finalize())
 ctx.set_camera(orbit_camera(w, h, **camkw))
 # the form is forced: under ncu every launch is replayed and serialised, so spk_cuda_choose_tracer's timings mean nothing
-# there. 1162 is what it picks for this scene in a plain run (bench.py prints config.megakernel_form).
-FORM = int(os.environ.get("SPK_FORM", 1162))
+# there. 1084 is what it picks for this scene in a plain run (bench.py prints config.megakernel_form).
+FORM = int(os.environ.get("SPK_FORM", 1084))
 ctx.set_option(A.OPT_MEGAKERNEL_FORM, FORM)
 print("form", (0, FORM))
 for k in range(2):
