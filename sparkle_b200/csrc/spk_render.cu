@@ -233,24 +233,24 @@ __global__ void __launch_bounds__(WARPS * 32, MINB)
             }
             else
             {
-                    // CPURenderer.cpp:442-443, unsigned wrap
-                    const uint32_t frame_seed = a.first_sample + s * a.sample_stride;
-                    rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
-                    float u = ((float)i + rng_unit(rng)) * pw;
-                    float v = ((float)j + rng_unit(rng)) * ph;
-                    // SetupViewRay
-                    float dx, dy;
-                    unit_disk(rng, dx, dy);
-                    dx = dx * cam.aperture_radius;
-                    dy = dy * cam.aperture_radius;
-                    origin = cpos + (dx * cright + dy * cup);
-                    V3 target = lower_left + u * max_u + v * max_v;
-                    dir = normalized(target - origin);
-                    throughput = mk(1.f, 1.f, 1.f);
-                    color = mk(0.f, 0.f, 0.f);
-                    valid = 1.f;
-                    bounce = 0;
-need_path = false;
+                // CPURenderer.cpp:442-443, unsigned wrap
+                const uint32_t frame_seed = a.first_sample + s * a.sample_stride;
+                rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+                float u = ((float)i + rng_unit(rng)) * pw;
+                float v = ((float)j + rng_unit(rng)) * ph;
+                // SetupViewRay
+                float dx, dy;
+                unit_disk(rng, dx, dy);
+                dx = dx * cam.aperture_radius;
+                dy = dy * cam.aperture_radius;
+                origin = cpos + (dx * cright + dy * cup);
+                V3 target = lower_left + u * max_u + v * max_v;
+                dir = normalized(target - origin);
+                throughput = mk(1.f, 1.f, 1.f);
+                color = mk(0.f, 0.f, 0.f);
+                valid = 1.f;
+                bounce = 0;
+                need_path = false;
             }
         }
         if (!__syncthreads_or(live))
@@ -259,13 +259,13 @@ need_path = false;
         }
         // ---- phase B: one path segment
         bool done = false;
-            Hit hit;
-            hit.inst = SPK_INVALID_ID;
-            if (live && a.max_bounce != 0u)
-            {
-                trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
-                rays++;
-            }
+        Hit hit;
+        hit.inst = SPK_INVALID_ID;
+        if (live && a.max_bounce != 0u)
+        {
+            trace_closest<CULL, COUNT>(sc, origin, dir, hit, stack, cnt);
+            rays++;
+        }
         if (SYNC2)
         {
             __syncthreads();
@@ -273,86 +273,86 @@ need_path = false;
         // ---- phase C: shade it
         if (live)
         {
-                if (a.max_bounce == 0u)
+            if (a.max_bounce == 0u)
+            {
+                done = true; // a zero-iteration bounce loop: the sample is black and valid
+            }
+            else if (hit.inst == SPK_INVALID_ID)
+            {
+                if (sc.sky.has_sky)
                 {
-                    done = true; // a zero-iteration bounce loop: the sample is black and valid
+                    color = color + cmul(sky_evaluate(sc, dir), throughput);
                 }
-                else if (hit.inst == SPK_INVALID_ID)
+                done = true;
+            }
+            else
+            {
+                Surface sf;
+                get_intersection(sc, origin, dir, hit, sf);
+                V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
+                if (a.debug)
                 {
-                    if (sc.sky.has_sky)
-                    {
-                        color = color + cmul(sky_evaluate(sc, dir), throughput);
-                    }
+                    // parity probes (tests only): first-hit normal / tangent / (u, v, t)
+                    color = a.debug == 1 ? sf.normal : a.debug == 2 ? sf.tangent : mk(sf.u, sf.v, hit.t);
+                    done = true;
+                }
+                else if (norm(emissive) > kEps)
+                {
+                    color = color + cmul(emissive, throughput);
                     done = true;
                 }
                 else
                 {
-                    Surface sf;
-                    get_intersection(sc, origin, dir, hit, sf);
-                    V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
-                    if (a.debug)
+                    V3 next_dir;
+                    V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
+                    throughput = cmul(throughput, this_throughput);
+                    if (sqnorm(throughput) < kEps)
                     {
-                        // parity probes (tests only): first-hit normal / tangent / (u, v, t)
-                        color = a.debug == 1 ? sf.normal : a.debug == 2 ? sf.tangent : mk(sf.u, sf.v, hit.t);
-                        done = true;
-                    }
-                    else if (norm(emissive) > kEps)
-                    {
-                        color = color + cmul(emissive, throughput);
+                        valid = -1.f;
                         done = true;
                     }
                     else
                     {
-                        V3 next_dir;
-                        V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
-                        throughput = cmul(throughput, this_throughput);
-                        if (sqnorm(throughput) < kEps)
+                        if (bounce >= 3)
                         {
-                            valid = -1.f;
-                            done = true;
+                            float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
+                            p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
+                            if (rng_unit(rng) > p)
+                            {
+                                done = true;
+                            }
+                            else
+                            {
+                                throughput = throughput / p;
+                            }
                         }
-                        else
+                        if (!done)
                         {
-                            if (bounce >= 3)
-                            {
-                                float p = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
-                                p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p); // std::clamp
-                                if (rng_unit(rng) > p)
-                                {
-                                    done = true;
-                                }
-                                else
-                                {
-                                    throughput = throughput / p;
-                                }
-                            }
-                            if (!done)
-                            {
-                                origin = sf.location + next_dir * kTolerance;
-                                dir = next_dir;
-                                bounce++;
-                                done = bounce >= a.max_bounce; // the bounce cap adds nothing (CPURenderer.cpp:256)
-                            }
+                            origin = sf.location + next_dir * kTolerance;
+                            dir = next_dir;
+                            bounce++;
+                            done = bounce >= a.max_bounce; // the bounce cap adds nothing (CPURenderer.cpp:256)
                         }
                     }
                 }
-                if (done)
+            }
+            if (done)
+            {
+                color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
+                if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
                 {
-                    color = mk(fminf(color.x, a.output_limit), fminf(color.y, a.output_limit), fminf(color.z, a.output_limit));
-                    if (a.accum_mode == SPK_ACCUM_RUNNING_AVERAGE)
-                    {
-                        uint32_t n = min(a.cumulated + s, a.cumulated_cap);
-                        float ma = (float)n / (float)(n + 1u);
-                        acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
-                                          lerp1(valid, acc.w, ma));
-                    }
-                    else
-                    {
-                        acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
-                    }
-                    s++;
-                    need_path = true;
+                    uint32_t n = min(a.cumulated + s, a.cumulated_cap);
+                    float ma = (float)n / (float)(n + 1u);
+                    acc = make_float4(lerp1(color.x, acc.x, ma), lerp1(color.y, acc.y, ma), lerp1(color.z, acc.z, ma),
+                                      lerp1(valid, acc.w, ma));
                 }
+                else
+                {
+                    acc = make_float4(acc.x + color.x, acc.y + color.y, acc.z + color.z, acc.w + valid);
+                }
+                s++;
+                need_path = true;
+            }
         }
     }
     if (in_image)
