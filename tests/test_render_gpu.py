@@ -186,3 +186,36 @@ def test_spatial_denoise(oracle):
     assert (rel[changed] < 1e-4).mean() > 0.97, rel[changed]
     assert np.array_equal(gpu[..., 3][changed], ref[..., 3][changed])
     ctx.close()
+
+
+def test_cost_ordered_strips_do_not_change_the_image():
+    """the sorted megakernel launches its strips of tiles in the order of their cost in the previous launch (longest
+    first): a schedule only - every launch order gives the same image bit for bit, for both CTA shapes, also when the
+    order was learnt on another camera and another scene of the same resolution"""
+    w, h, spp = 640, 360, 8
+    sb, camkw = scenes.testscene()
+    desc = sb.finalize()
+    ctx = CudaContext(w, h)
+    ctx.upload_scene(desc)
+    ctx.set_camera(orbit_camera(w, h, **camkw))
+    for form in (1084, 1162):
+        ctx.set_option(A.OPT_MEGAKERNEL_FORM, form)
+        ctx.set_option(A.OPT_COST_ORDERED_STRIPS, 0)
+        ctx.reset_accumulation()
+        ctx.render(0, spp, max_bounce=8)
+        plain = ctx.resolve(A.RESOLVE_LINEAR_F32)
+        ctx.set_option(A.OPT_COST_ORDERED_STRIPS, 1)
+        for launch in range(3):  # the first learns the costs, the next two run in cost order
+            ctx.reset_accumulation()
+            ctx.render(0, spp, max_bounce=8)
+            assert np.array_equal(ctx.resolve(A.RESOLVE_LINEAR_F32), plain), (form, launch)
+    # a stale order (learnt above) on another view and another scene: still only a schedule
+    ctx.set_camera(orbit_camera(w, h, **dict(camkw, yaw=70.0, pitch=35.0)))
+    ctx.reset_accumulation()
+    ctx.render(0, spp, max_bounce=8)
+    moved = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    ctx.set_option(A.OPT_COST_ORDERED_STRIPS, 0)
+    ctx.reset_accumulation()
+    ctx.render(0, spp, max_bounce=8)
+    assert np.array_equal(ctx.resolve(A.RESOLVE_LINEAR_F32), moved)
+    ctx.close()
