@@ -154,7 +154,10 @@ __global__ void __launch_bounds__(kExtendWarps * 32)
     const uint32_t *__restrict__ queue = st.queue[q];
     const float4 *__restrict__ rays = st.rays;
     TraceCounters cnt{0, 0, 0, 0};
-    warp_trace_loop<CULL, COUNT, REFILL, 8>(
+#ifndef SPK_WF_VOTE
+#define SPK_WF_VOTE 8
+#endif
+    warp_trace_loop<CULL, COUNT, REFILL, SPK_WF_VOTE>(
         sc, st.ctrl->n_queue[q], &st.ctrl->next_ray, s_lane_words, cnt,
         [&](unsigned long long id, V3 &o, V3 &d) {
             const uint32_t slot = __ldg(queue + id);
@@ -388,7 +391,10 @@ static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st)
 template <bool CULL, bool COUNT>
 static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t sample_count)
 {
-    auto extend = wf_extend_kernel<CULL, COUNT, 4>;
+#ifndef SPK_WF_REFILL
+#define SPK_WF_REFILL 8
+#endif
+    auto extend = wf_extend_kernel<CULL, COUNT, SPK_WF_REFILL>;
     static int blocks_per_sm = 0, sms = 0;
     if (blocks_per_sm == 0)
     {
