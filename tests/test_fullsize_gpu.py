@@ -89,8 +89,8 @@ def test_c2_full_resolution(oracle, monkeypatch):
 
 
 def test_c2_megakernel_forms_agree():
-    """phased, sorted 16x2 and sorted 8x4 are the same arithmetic in the same order (SPK_RENDER_PHASED is read once per
-    process, so the forms are compared through spk_cuda_choose_tracer's candidates on one context)"""
+    """the megakernel forms are the same arithmetic in the same order: whatever form spk_cuda_choose_tracer measures
+    fastest gives the image the default form gave, bit for bit"""
     w, h = 640, 360
     sb, camkw = scenes.room(num_objects=20, tex=64)
     ctx = CudaContext(w, h)

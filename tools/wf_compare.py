@@ -1,5 +1,5 @@
 """Megakernel vs wavefront (SPK_FLAG_WAVEFRONT) on the bench scenes: CUDA-event time of the whole render call.
-usage: wf_compare.py [scene ...]   scenes: testscene city room ; env SPK_SPP, SPK_WF_SLOTS"""
+usage: wf_compare.py [scene ...]   scenes: testscene city room ; env SPK_SPP, SPK_WF_SLOTS_LIST"""
 import os, sys, time
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 import numpy as np
@@ -38,7 +38,7 @@ for name in names:
     img_m = ctx.resolve(A.RESOLVE_LINEAR_F32)
     print(f"{name} megakernel {spp} spp: {ms:.2f} ms  {w*h*spp/ms/1e3:.0f} Mpaths/s  {st['rays']/ms/1e3:.0f} Mrays/s rays/path {st['rays']/st['paths']:.2f}", flush=True)
     for slots in os.environ.get("SPK_WF_SLOTS_LIST", "524288,1048576,2097152,4194304").split(","):
-        os.environ["SPK_WF_SLOTS"] = slots
+        ctx.set_option(A.OPT_WAVEFRONT_SLOTS, int(slots))
         ms, st = run(A.FLAG_WAVEFRONT)
         img_w = ctx.resolve(A.RESOLVE_LINEAR_F32)
         err = float(np.abs(img_w - img_m).max())

@@ -11,7 +11,7 @@ ctx.set_stream(torch.cuda.current_stream().cuda_stream)
 ctx.upload_scene(sb.finalize())
 ctx.set_camera(orbit_camera(w, h, **camkw))
 for slots in (1 << 20, 1 << 21, 1 << 22, 1 << 23, 1 << 24):
-    os.environ["SPK_WF_SLOTS"] = str(slots)
+    ctx.set_option(A.OPT_WAVEFRONT_SLOTS, slots)
     best = 1e9
     for k in range(2):
         ctx.reset_accumulation()
