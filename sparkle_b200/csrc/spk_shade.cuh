@@ -245,8 +245,13 @@ template <typename T> __device__ __forceinline__ float bary(T v0, T v1, T v2, fl
     return v0 + (v1 - v0) * u + (v2 - v0) * v; // utilities::Lerp(v0, v1, v2, u, v)
 }
 
+#ifdef SPK_NOINLINE_NMAP
+static __device__ __noinline__ void material_normal_texture(const DScene &sc, const DMaterial &m, float tu, float tv,
+                                                            V3 tangent, float headedness, V3 &n)
+#else
 __device__ __forceinline__ void material_normal_texture(const DScene &sc, const DMaterial &m, float tu, float tv,
                                                         V3 tangent, float headedness, V3 &n)
+#endif
 {
     // MaterialRenderProxy::GetNormal = Sample(uv) * 2 - Ones; utilities::TangentSpaceToWorldSpace
     V3 s = sample_texture(sc.textures[m.normal_tex], tu, tv);
@@ -403,6 +408,53 @@ __device__ __forceinline__ void local_axes(V3 normal, V3 tangent, V3 &u, V3 &v, 
 }
 
 // MaterialRenderProxy::SampleSurface for Pbr / Dielectric; returns this bounce's throughput, sets wi (world)
+// DieletricBxDF::Sample (BxDF.h:112-141), FrDielectric (Utilities.h:301-324), EtaI = 1
+#ifdef SPK_NOINLINE_DIEL
+static __device__ __noinline__ V3 dielectric_sample(float eta, V3 lwo, Rng &rng)
+#else
+__device__ __forceinline__ V3 dielectric_sample(float eta, V3 lwo, Rng &rng)
+#endif
+{
+    V3 lwi;
+    float cos_i = lwo.z, eta_i = 1.f, eta_t = eta;
+    if (!(cos_i > 0.f))
+    {
+        eta_i = eta;
+        eta_t = 1.f;
+        cos_i = -cos_i;
+    }
+    float sin_i = sqrtf(1.f - cos_i * cos_i);
+    float ref_idx = eta_i / eta_t;
+    float sin_t = ref_idx * sin_i;
+    float fresnel;
+    if (sin_t >= 1.f)
+    {
+        fresnel = 1.f;
+    }
+    else
+    {
+        float r0 = (1.f - ref_idx) / (1.f + ref_idx);
+        r0 = r0 * r0;
+        fresnel = schlick1(cos_i, r0);
+    }
+    if (rng_unit(rng) < fresnel)
+    {
+        lwi = mk(-lwo.x, -lwo.y, lwo.z); // utilities::Reflect(w)
+    }
+    else
+    {
+        bool entering = lwo.z > 0.f;
+        float ratio = entering ? 1.f / eta : eta / 1.f;
+        // utilities::Refract
+        float ct = lwo.z;
+        float sin_i2 = 1.f - ct * ct;
+        float sin_t2 = ratio * ratio * sin_i2;
+        float cos_t = sqrtf(1.f - sin_t2) * (ct > 0.f ? -1.f : 1.f);
+        lwi = normalized(mk(-ratio * lwo.x, -ratio * lwo.y, cos_t));
+    }
+    return lwi;
+}
+
 __device__ __forceinline__ V3 sample_surface(const DScene &sc, Rng &rng, const Surface &sf, V3 ray_dir, V3 &wi_world)
 {
     const DMaterial &m = sc.materials[sf.material];
@@ -415,44 +467,7 @@ __device__ __forceinline__ V3 sample_surface(const DScene &sc, Rng &rng, const S
     V3 throughput;
     if (__ldg(&m.type) == 1u)
     {
-        // DieletricBxDF::Sample (BxDF.h:112-141), FrDielectric (Utilities.h:301-324), EtaI = 1
-        float eta = __ldg(&m.eta);
-        float cos_i = lwo.z, eta_i = 1.f, eta_t = eta;
-        if (!(cos_i > 0.f))
-        {
-            eta_i = eta;
-            eta_t = 1.f;
-            cos_i = -cos_i;
-        }
-        float sin_i = sqrtf(1.f - cos_i * cos_i);
-        float ref_idx = eta_i / eta_t;
-        float sin_t = ref_idx * sin_i;
-        float fresnel;
-        if (sin_t >= 1.f)
-        {
-            fresnel = 1.f;
-        }
-        else
-        {
-            float r0 = (1.f - ref_idx) / (1.f + ref_idx);
-            r0 = r0 * r0;
-            fresnel = schlick1(cos_i, r0);
-        }
-        if (rng_unit(rng) < fresnel)
-        {
-            lwi = mk(-lwo.x, -lwo.y, lwo.z); // utilities::Reflect(w)
-        }
-        else
-        {
-            bool entering = lwo.z > 0.f;
-            float ratio = entering ? 1.f / eta : eta / 1.f;
-            // utilities::Refract
-            float ct = lwo.z;
-            float sin_i2 = 1.f - ct * ct;
-            float sin_t2 = ratio * ratio * sin_i2;
-            float cos_t = sqrtf(1.f - sin_t2) * (ct > 0.f ? -1.f : 1.f);
-            lwi = normalized(mk(-ratio * lwo.x, -ratio * lwo.y, cos_t));
-        }
+        lwi = dielectric_sample(__ldg(&m.eta), lwo, rng);
         throughput = ms.base_color;
     }
     else
