@@ -407,6 +407,18 @@ int spk_cuda_destroy(SpkContext *ctx)
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_rays);
     cudaFree(ctx->d_hits);
+    if (ctx->copy_in_stream)
+    {
+        cudaStreamDestroy(ctx->copy_in_stream);
+        cudaStreamDestroy(ctx->copy_out_stream);
+        for (cudaEvent_t e : ctx->pipe_ev)
+        {
+            if (e)
+            {
+                cudaEventDestroy(e);
+            }
+        }
+    }
     cudaFree(ctx->d_resolve);
     cudaFree(ctx->wf_block);
     cudaFree(ctx->d_group_block);

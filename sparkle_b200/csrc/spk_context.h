@@ -51,6 +51,9 @@ struct SpkContext
     void *d_rays = nullptr;
     void *d_hits = nullptr;
     size_t ray_capacity = 0;
+    // pinned host buffers: copy-in / copy-out streams and events of the three-stage pipeline (spk_cuda_trace_closest)
+    cudaStream_t copy_in_stream = nullptr, copy_out_stream = nullptr;
+    cudaEvent_t pipe_ev[16] = {};
 
     void *d_resolve = nullptr;
     size_t resolve_capacity = 0;

@@ -9,6 +9,7 @@
  */
 #include "spk_context.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include "spk_traverse.cuh"
 #include "spk_traverse_warp.cuh"
@@ -260,6 +261,57 @@ int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_ray
         SPK_CUDA_TRY(cudaMalloc(&ctx->d_rays, num_rays * sizeof(SpkRay)));
         SPK_CUDA_TRY(cudaMalloc(&ctx->d_hits, num_rays * sizeof(SpkHit)));
         ctx->ray_capacity = num_rays;
+    }
+    // Page-locked host buffers (spk_cuda_host_alloc, cudaHostAlloc, pinned torch tensors): a three-stage pipeline over
+    // pieces of 2 Mi rays - copy-in, traversal and copy-out on three streams - so the two PCIe directions and the kernel
+    // overlap; the call is then bound by the slower direction (32 B in per ray) instead of the sum of all three.
+    auto is_pinned = [](const void *p) {
+        cudaPointerAttributes attr{};
+        const bool yes = cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        return yes;
+    };
+    constexpr uint64_t kPiece = 2u << 20;
+    if (num_rays >= 2 * kPiece && is_pinned(rays) && is_pinned(hits))
+    {
+        if (!ctx->copy_in_stream)
+        {
+            SPK_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_in_stream, cudaStreamNonBlocking));
+            SPK_CUDA_TRY(cudaStreamCreateWithFlags(&ctx->copy_out_stream, cudaStreamNonBlocking));
+            for (int k = 0; k < 8; k++)
+            {
+                SPK_CUDA_TRY(cudaEventCreateWithFlags(&ctx->pipe_ev[k], cudaEventDisableTiming));
+                SPK_CUDA_TRY(cudaEventCreateWithFlags(&ctx->pipe_ev[8 + k], cudaEventDisableTiming));
+            }
+        }
+        // the copy-in stream starts where the context's stream is now (earlier work may still be using the buffers)
+        SPK_CUDA_TRY(cudaEventRecord(ctx->pipe_ev[0], ctx->stream));
+        SPK_CUDA_TRY(cudaStreamWaitEvent(ctx->copy_in_stream, ctx->pipe_ev[0], 0));
+        SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+        uint64_t piece = 0;
+        for (uint64_t at = 0; at < num_rays; at += kPiece, piece++)
+        {
+            const uint64_t n = std::min<uint64_t>(kPiece, num_rays - at);
+            cudaEvent_t in_done = ctx->pipe_ev[piece % 8], traced = ctx->pipe_ev[8 + piece % 8];
+            SPK_CUDA_TRY(cudaMemcpyAsync(static_cast<SpkRay *>(ctx->d_rays) + at, rays + at, n * sizeof(SpkRay),
+                                         cudaMemcpyHostToDevice, ctx->copy_in_stream));
+            SPK_CUDA_TRY(cudaEventRecord(in_done, ctx->copy_in_stream));
+            SPK_CUDA_TRY(cudaStreamWaitEvent(ctx->stream, in_done, 0));
+            int rc = launch_trace_closest(ctx, static_cast<SpkRay *>(ctx->d_rays) + at, n, static_cast<SpkHit *>(ctx->d_hits) + at,
+                                          flags);
+            if (rc != SPK_OK)
+            {
+                return rc;
+            }
+            SPK_CUDA_TRY(cudaEventRecord(traced, ctx->stream));
+            SPK_CUDA_TRY(cudaStreamWaitEvent(ctx->copy_out_stream, traced, 0));
+            SPK_CUDA_TRY(cudaMemcpyAsync(hits + at, static_cast<SpkHit *>(ctx->d_hits) + at, n * sizeof(SpkHit),
+                                         cudaMemcpyDeviceToHost, ctx->copy_out_stream));
+        }
+        SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
+        SPK_CUDA_TRY(cudaStreamSynchronize(ctx->copy_out_stream));
+        SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        return SPK_OK;
     }
     SPK_CUDA_TRY(cudaMemcpyAsync(ctx->d_rays, rays, num_rays * sizeof(SpkRay), cudaMemcpyHostToDevice, ctx->stream));
     SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));

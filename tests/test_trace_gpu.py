@@ -129,3 +129,30 @@ def test_update_instances_validation_and_extent(oracle):
     assert_hits_equal(ctx.trace_closest(rays, A.FLAG_EXACT_TRAVERSAL), ref, "moved, exact")
     assert_hits_equal(ctx.trace_closest(rays), ref, "moved, culled")
     ctx.close()
+
+
+def test_pinned_host_buffers_take_the_pipelined_path():
+    """spk_cuda_trace_closest with page-locked host buffers overlaps copy-in, traversal and copy-out in pieces of 2 Mi rays:
+    the hits are those of the one-shot path (pageable buffers), bit for bit, including a ragged last piece"""
+    import ctypes as C
+    sb, _ = scenes.testscene()
+    ctx = CudaContext(64, 64)
+    ctx.upload_scene(sb.finalize())
+    n = (5 << 20) + 12345
+    rays = geometry.random_rays(n, seed=21, extent=14.0)
+    plain = ctx.trace_closest(rays)
+    lib = ctx.lib
+    p_rays, p_hits = C.c_void_p(), C.c_void_p()
+    A.check(lib.spk_cuda_host_alloc(C.byref(p_rays), rays.nbytes))
+    A.check(lib.spk_cuda_host_alloc(C.byref(p_hits), n * 20))
+    C.memmove(p_rays.value, rays.ctypes.data, rays.nbytes)
+    A.check(lib.spk_cuda_trace_closest(ctx.handle, p_rays, n, p_hits, 0))
+    piped = np.frombuffer((C.c_uint8 * (n * 20)).from_address(p_hits.value), dtype=plain.dtype).copy()
+    for f in ("prim", "face"):
+        assert np.array_equal(piped[f], plain[f])
+    for f in ("t", "u", "v"):
+        assert np.array_equal(piped[f].view(np.uint32), plain[f].view(np.uint32))
+    assert ctx.stats()["last_ms"] > 0
+    lib.spk_cuda_host_free(p_rays)
+    lib.spk_cuda_host_free(p_hits)
+    ctx.close()
