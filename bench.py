@@ -15,6 +15,8 @@ seeds as the reference CPU path tracer. One STEP = one full render of that image
           rank 0 checks the combined frame against a single-context render of the same samples.
   extra   the other configs BASELINE.json names, in the same JSON line at every N: c3 (soup-1M, 64 Mi incoherent rays) and
           its coherent counterpart (terrain-1M, 64 Mi camera rays), c4 (city-10M at 4K, bounded spp), c5 (room, depth 32).
+  gpu_launches   this repo's kernels launched inside the timed steps (1 render kernel per step, +1 group kernel at N > 1;
+          cub's radix-sort kernels that order the next launch's strips are library kernels and are not counted).
   roofline   dominant kernel, HBM bound by contract: algorithmic bytes (SURVEY.md 8d / DESIGN.md) from the kernel's own
           counters. `traffic` is the measured DRAM traffic of the same launch from the committed ncu pass when the launch
           matches it; `dram_frac` is that traffic over time over peak - the honest HBM utilisation figure.

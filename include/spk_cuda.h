@@ -327,6 +327,7 @@ int spk_cuda_group_resolve(SpkGroup *group, uint32_t format, uint32_t total_samp
 /* IPC groups: by default ranks > 0 return from spk_cuda_group_resolve when their kernel has finished (so a rank that
  * never joined is reported to everyone); enabled = 1 makes them return at once, like the root with host_out == NULL. */
 int spk_cuda_group_set_async(SpkGroup *group, uint32_t enabled);
+/* Destroy a group BEFORE the contexts it was made from. */
 int spk_cuda_group_destroy(SpkGroup *group);
 
 /* Tuning knobs, explicit (nothing in the library reads the environment). Defaults are the measured choices. */
