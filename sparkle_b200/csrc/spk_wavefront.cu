@@ -147,7 +147,10 @@ __global__ void wf_advance_kernel(WfState st, uint32_t cur, unsigned long long *
 
 // ---- extend: closest hit of every queued ray; the loop of trace_persistent_kernel (spk_trace.cu) over an indirect queue
 template <bool CULL, bool COUNT, int REFILL>
-__global__ void __launch_bounds__(kExtendWarps * 32)
+#ifndef SPK_WF_EXTEND_CTAS
+#define SPK_WF_EXTEND_CTAS 8 // 64 registers instead of 72: 8 CTAs per SM instead of 7 (city-10M 4K x 16 spp: 403 -> 385 ms)
+#endif
+__global__ void __launch_bounds__(kExtendWarps * 32, SPK_WF_EXTEND_CTAS)
     wf_extend_kernel(const DScene sc, WfState st, uint32_t q, unsigned long long *__restrict__ counters)
 {
     __shared__ uint32_t s_lane_words[kExtendWarps * kLaneSmemWords * 32];
@@ -188,7 +191,10 @@ __global__ void __launch_bounds__(kExtendWarps * 32)
 }
 
 // ---- shade: SamplePixel's loop body after Intersect (CPURenderer.cpp:259-369) for every traced slot
-__global__ void __launch_bounds__(kShadeThreads)
+#ifndef SPK_WF_SHADE_CTAS
+#define SPK_WF_SHADE_CTAS 1
+#endif
+__global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     wf_shade_kernel(const DScene sc, const WfArgs a, WfState st, uint32_t cur, float4 *__restrict__ accum)
 {
     __shared__ uint32_t s_bin[32];
