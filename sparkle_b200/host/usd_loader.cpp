@@ -801,11 +801,6 @@ struct Converter
         }
         const UsdProperty *points = prim.Prop("points"), *normals = prim.Prop("normals");
         const UsdProperty *counts = prim.Prop("faceVertexCounts"), *indices = prim.Prop("faceVertexIndices");
-        if (!points || !indices || points->value.numbers.empty() || points->value.numbers.size() % 3 != 0 ||
-            indices->value.numbers.empty() || indices->value.numbers.size() % 3 != 0)
-        {
-            return Fail("Mesh " + prim.name + " needs points and triangle faceVertexIndices");
-        }
         if (counts)
         {
             for (double c : counts->value.numbers)
@@ -817,6 +812,11 @@ struct Converter
                     return true;
                 }
             }
+        }
+        if (!points || !indices || points->value.numbers.empty() || points->value.numbers.size() % 3 != 0 ||
+            indices->value.numbers.empty() || indices->value.numbers.size() % 3 != 0)
+        {
+            return Fail("Mesh " + prim.name + " needs points and triangle faceVertexIndices");
         }
         const size_t nv = points->value.numbers.size() / 3;
         if (!normals || normals->value.numbers.size() != nv * 3)

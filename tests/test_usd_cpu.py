@@ -144,3 +144,68 @@ def test_round_trip_equals_the_source_scene(tmp_path, kind):
     rel = np.abs(img_a[..., :3] - img_b[..., :3]).sum(-1) / np.maximum(img_b[..., :3].sum(-1), 1e-3)
     assert np.median(rel) < 1e-4
     A.host_lib().spk_host_scene_free(s)
+
+
+def test_reader_accepts_the_syntax_variants_of_usda(tmp_path):
+    """comments, doc strings, `custom` / `uniform` qualifiers, scientific notation, float3 tangents (w = 1), a node without
+    an xformOp (identity), a quad mesh (skipped like a non-single-indexable one), unknown prim types (skipped with a log)"""
+    text = '''#usda 1.0
+(
+    doc = """multi
+line"""
+    defaultPrim = "World"
+)
+def Xform "World" (
+    kind = "component"
+    customData = { string note = "braces { inside } a string" }
+)
+{
+    def Xform "n" {
+        custom float userProperties:x = 1.5e0
+        def Mesh "tri" (
+            prepend apiSchemas = ["MaterialBindingAPI"]
+        )
+        {
+            uniform token subdivisionScheme = "none"
+            int[] faceVertexCounts = [3]
+            int[] faceVertexIndices = [0, 1, 2]
+            rel material:binding = </World/Looks/m>
+            normal3f[] normals = [(0, 0, 1), (0, 0, 1), (0, 0, 1)]
+            point3f[] points = [(0, 0, 0), (1e0, 0, 0), (0, 2.5E-1, 0)]  # a comment after a value
+            float3[] primvars:tangents = [(0, 1, 0), (0, 1, 0), (0, 1, 0)]
+        }
+        def Mesh "quad" {
+            int[] faceVertexCounts = [4]
+            int[] faceVertexIndices = [0, 1, 2, 3]
+            rel material:binding = </World/Looks/m>
+            normal3f[] normals = [(0, 0, 1), (0, 0, 1), (0, 0, 1), (0, 0, 1)]
+            point3f[] points = [(0, 0, 0), (1, 0, 0), (1, 1, 0), (0, 1, 0)]
+        }
+        def SphereLight "unsupported" { float inputs:radius = 1 }
+    }
+    def Scope "Looks" {
+        def Material "m" {
+            def Shader "s" {
+                uniform token info:id = "UsdPreviewSurface"
+                color3f inputs:diffuseColor = (0.25, 0.5, 0.75)
+            }
+        }
+    }
+}
+'''
+    path = tmp_path / "variants.usda"
+    path.write_text(text)
+    st = probe(path)
+    assert st["meshes"] == 1 and st["skipped"] == 1 and st["materials"] == 1 and st["nodes"] == 2
+    s, desc, _ = load(path)
+    fwd = np.array(list(desc.primitives[0].fwd), np.float32).reshape(3, 4)
+    assert np.array_equal(fwd, np.eye(4, dtype=np.float32)[:3])  # no xformOp anywhere: identity
+    tang = np.ctypeslib.as_array(desc.meshes[0].tangents, shape=(3, 4))
+    assert np.array_equal(tang, np.tile(np.array([0, 1, 0, 1], np.float32), (3, 1)))
+    verts = np.ctypeslib.as_array(desc.meshes[0].vertices, shape=(3, 3))
+    assert np.array_equal(verts, np.array([[0, 0, 0], [1, 0, 0], [0, 0.25, 0]], np.float32))
+    m = desc.materials[0]
+    # UsdPreviewSurface fallbacks for inputs that are not authored: metallic 0, roughness 0.5, opaque -> PBR
+    assert m.type == A.MAT_PBR and list(m.base_color) == [0.25, 0.5, 0.75]
+    assert np.float32(m.metallic) == 0 and np.float32(m.roughness) == np.float32(0.5)
+    A.host_lib().spk_host_scene_free(s)
