@@ -1065,10 +1065,29 @@ uint64_t scene_stamp(const SpkSceneDesc *d)
     mix(reinterpret_cast<uint64_t>(d->primitives));
     mix(reinterpret_cast<uint64_t>(d->meshes));
     mix(reinterpret_cast<uint64_t>(d->tlas.nodes));
+    // addresses are not an identity (freed tables are handed out again): the heads of the cached tables by content too
+    auto bytes = [&](const void *p, size_t n) {
+        const auto *b = static_cast<const uint8_t *>(p);
+        for (size_t k = 0; p && k < n; k++)
+        {
+            mix(b[k]);
+        }
+    };
+    auto tree = [&](const SpkBvhDesc &t) {
+        mix(t.num_nodes);
+        mix(t.num_prims);
+        bytes(t.nodes, size_t(std::min<uint32_t>(t.num_nodes, 16u)) * t.node_stride);
+        bytes(t.prim_ids, size_t(std::min<uint32_t>(t.num_prims, 64u)) * t.prim_id_bytes);
+    };
+    tree(d->tlas);
     for (uint32_t m = 0; m < d->num_meshes; m++)
     {
         mix(reinterpret_cast<uint64_t>(d->meshes[m].vertices));
         mix(d->meshes[m].num_faces);
+        mix(d->meshes[m].num_vertices);
+        bytes(d->meshes[m].vertices, size_t(std::min<uint32_t>(d->meshes[m].num_vertices, 32u)) * 12);
+        bytes(d->meshes[m].indices, size_t(std::min<uint32_t>(d->meshes[m].num_faces, 32u)) * 12);
+        tree(d->meshes[m].blas);
     }
     return h;
 }

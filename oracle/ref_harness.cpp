@@ -172,22 +172,67 @@ std::unique_ptr<RefScene> g_scene;
 
 uint64_t SceneFingerprint(const SpkSceneDesc *d)
 {
-    // cheap identity so repeated calls with the same descriptor reuse the built reference scene
+    // identity of a scene so that repeated calls with the same descriptor reuse the built reference scene. Addresses
+    // alone are NOT an identity (a freed descriptor's memory is handed out again: a second TestScene with a cube-map sky
+    // once came back as the cached gradient-sky one), so every table is hashed by CONTENT: all primitives, materials,
+    // texture and sky descriptors with the head of their pixels, mesh descriptors with the head of their arrays, the
+    // head of every tree.
     uint64_t h = 1469598103934665603ull;
     auto mix = [&h](uint64_t v) { h = (h ^ v) * 1099511628211ull; };
+    auto bytes = [&](const void *p, size_t n) {
+        const auto *b = static_cast<const uint8_t *>(p);
+        for (size_t k = 0; p && k < n; k++)
+        {
+            mix(b[k]);
+        }
+    };
+    auto texel_bytes = [](uint32_t format) -> size_t {
+        return format == SPK_FMT_RGBA32F ? 16 : format == SPK_FMT_RGBA16F ? 8 : 4;
+    };
+    auto texture = [&](const SpkTextureDesc &t) {
+        mix(t.width);
+        mix(t.height);
+        mix(t.format);
+        const size_t total = size_t(t.width) * t.height * texel_bytes(t.format);
+        bytes(t.pixels, std::min<size_t>(total, 256));
+        if (t.pixels && total > 512)
+        {
+            bytes(static_cast<const uint8_t *>(t.pixels) + total - 256, 256);
+        }
+    };
+    auto tree = [&](const SpkBvhDesc &t) {
+        mix(t.num_nodes);
+        mix(t.num_prims);
+        bytes(t.nodes, size_t(std::min<uint32_t>(t.num_nodes, 16u)) * t.node_stride);
+        bytes(t.prim_ids, size_t(std::min<uint32_t>(t.num_prims, 64u)) * t.prim_id_bytes);
+    };
     mix(reinterpret_cast<uint64_t>(d));
     mix(d->num_meshes);
     mix(d->num_primitives);
     mix(d->num_materials);
-    mix(reinterpret_cast<uint64_t>(d->primitives));
-    mix(reinterpret_cast<uint64_t>(d->tlas.nodes));
-    if (d->num_primitives)
+    mix(d->num_textures);
+    bytes(d->primitives, sizeof(SpkPrimitiveDesc) * size_t(d->num_primitives));
+    bytes(d->materials, sizeof(SpkMaterialDesc) * size_t(d->num_materials));
+    for (uint32_t t = 0; t < d->num_textures; t++)
     {
-        const auto *p = reinterpret_cast<const uint32_t *>(d->primitives);
-        for (size_t k = 0; k < sizeof(SpkPrimitiveDesc) / 4 * std::min<uint32_t>(d->num_primitives, 64u); k++)
-        {
-            mix(p[k]);
-        }
+        texture(d->textures[t]);
+    }
+    for (uint32_t m = 0; m < d->num_meshes; m++)
+    {
+        const SpkMeshDesc &md = d->meshes[m];
+        mix(md.num_vertices);
+        mix(md.num_faces);
+        bytes(md.vertices, size_t(std::min<uint32_t>(md.num_vertices, 32u)) * 12);
+        bytes(md.indices, size_t(std::min<uint32_t>(md.num_faces, 32u)) * 12);
+        tree(md.blas);
+    }
+    tree(d->tlas);
+    mix(d->sky.has_sky);
+    mix(d->sky.has_map);
+    bytes(d->sky.color, 12);
+    for (int f = 0; d->sky.has_sky && d->sky.has_map && f < 6; f++)
+    {
+        texture(d->sky.faces[f]);
     }
     return h;
 }

@@ -131,6 +131,12 @@ def test_cube_map_sky_image(oracle):
     gpu, _ = gpu_render(desc, cam, w, h, 0, spp, 8)
     ref, _ = oracle.render(desc, cam, w, h, 0, spp, max_bounce=8)
     m = PR.report("a14_cube_sky_testscene", gpu, ref / spp, dict(spp=spp))
+    if m["mean_rel"] > MEAN_REL_TOL:  # say which side moved: the device or the reference build
+        import oracle_lib as O
+        port, _ = O.Oracle("port").render(desc, cam, w, h, 0, spp, max_bounce=8)
+        again, _ = gpu_render(desc, cam, w, h, 0, spp, 8)
+        m["diag"] = dict(gpu_vs_port=float(np.abs(gpu - port / spp).mean()), ref_vs_port=float(np.abs(ref - port).mean() / spp),
+                         gpu_again_vs_gpu=float(np.abs(again - gpu).mean()))
     assert m["mean_rel"] <= MEAN_REL_TOL and m["psnr"] > 40.0, m
     # the committed golden image of the same scene (the pin that travels)
     import os
