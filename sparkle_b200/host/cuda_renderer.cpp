@@ -124,6 +124,10 @@ bool RenderConfig::Set(const std::string &name, const std::string &value)
     {
         ok = as_bool(device_tlas);
     }
+    else if (name == "device_bvh")
+    {
+        ok = as_bool(device_bvh);
+    }
     else if (name == "gpus")
     {
         ok = as_u32(gpus) && gpus >= 1 && gpus <= 16;
@@ -710,6 +714,20 @@ void CudaRenderer::Update()
     }
     const SpkSceneDesc &d = scene_render_proxy_->Desc();
     int rc = SPK_OK;
+    // device_bvh: the same descriptor with every tree left out, so that spk_cuda_upload_scene builds them on the device
+    SpkSceneDesc without_trees = d;
+    std::vector<SpkMeshDesc> meshes_without_trees;
+    if (render_config_.device_bvh)
+    {
+        meshes_without_trees.assign(d.meshes, d.meshes + d.num_meshes);
+        for (SpkMeshDesc &m : meshes_without_trees)
+        {
+            m.blas = SpkBvhDesc{};
+        }
+        without_trees.meshes = meshes_without_trees.data();
+        without_trees.tlas = SpkBvhDesc{};
+    }
+    const SpkSceneDesc &up = render_config_.device_bvh ? without_trees : d;
     for (SpkContext *c : ctxs_) // the scene is replicated on every GPU
     {
         if (rc != SPK_OK)
@@ -718,15 +736,16 @@ void CudaRenderer::Update()
         }
         if (structural)
         {
-            rc = spk_cuda_upload_scene(c, &d);
+            rc = spk_cuda_upload_scene(c, &up);
         }
         else if (moved)
         {
-            rc = spk_cuda_update_instances(c, d.primitives, d.num_primitives, render_config_.device_tlas ? nullptr : &d.tlas);
+            rc = spk_cuda_update_instances(c, d.primitives, d.num_primitives,
+                                           (render_config_.device_tlas || render_config_.device_bvh) ? nullptr : &d.tlas);
             if (rc != SPK_OK)
             {
                 // e.g. the rebuilt TLAS has more nodes than the uploaded one: a full upload always fits
-                rc = spk_cuda_upload_scene(c, &d);
+                rc = spk_cuda_upload_scene(c, &up);
             }
         }
     }

@@ -64,6 +64,9 @@ struct RenderConfig
     // PrimitiveChangeType::Update: rebuild the TLAS on the device (spk_cuda_update_instances with tlas == NULL) instead
     // of uploading the host-rebuilt one
     bool device_tlas = false;
+    // every BLAS and the TLAS are built on the device at upload (SpkBvhDesc.nodes == NULL, csrc/spk_build.cu) instead of
+    // uploading the host-built bvh::v2 trees
+    bool device_bvh = false;
     std::vector<int> gpu_devices;
 
     [[nodiscard]] bool IsCPURenderMode() const { return pipeline == Pipeline::Cpu; }

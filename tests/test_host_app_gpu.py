@@ -92,6 +92,23 @@ def test_primitive_move_with_device_side_tlas_rebuild(oracle):
     a.close()
 
 
+def test_device_built_trees_in_the_host_app(oracle):
+    """8f-4: --device_bvh true -> every BLAS and the TLAS are built on the device at upload (and rebuilt there on a
+    move); closest hits do not depend on the topology (exact-t ties apart), so the image matches the oracle walking the
+    host's trees"""
+    w, h, spp = 96, 64, 4
+    a = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 2 --spatial_denoise false "
+                    "--device_bvh true")
+    a.run(100)
+    ref, _ = oracle.render(a.scene, a.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
+    assert rel_err(a.read_linear(), ref) <= 1e-3
+    a.move_primitive(3, (2.0, -1.0, 3.5))
+    a.run(100)
+    ref, _ = oracle.render(a.scene, a.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
+    assert rel_err(a.read_linear(), ref) <= 1e-3
+    a.close()
+
+
 def test_gltf_scene_through_the_host_app(tmp_path, oracle):
     """8f-1: --scene file.gltf -> GLTFLoader semantics -> CudaRenderer; the image equals the oracle's on the app's own
     scene description"""
