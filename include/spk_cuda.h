@@ -48,7 +48,7 @@ typedef enum SpkStatus {
  * node 0 is the root. `node_stride` is 28 (the raw library struct) or 32 (padded). `prim_ids` maps
  * leaf slots to primitive indices (bvh_.prim_ids; 8-byte size_t in the library, 4-byte also accepted).
  * nodes == NULL with num_nodes == 0: the tree is BUILT ON THE DEVICE by spk_cuda_upload_scene (an LBVH: Morton sort,
- * Karras hierarchy, bottom-up fit, leaves of <= 4 triangles / 1 primitive; csrc/spk_build.cu) and can be read back with
+ * Karras hierarchy, bottom-up fit, one triangle / primitive per leaf by default; csrc/spk_build.cu) and can be read back with
  * spk_cuda_download_bvh.
  */
 typedef struct SpkBvhNode {
@@ -343,7 +343,7 @@ typedef enum SpkOption {
     SPK_OPT_SMEM_CARVEOUT = 4,   /* percent of the SM's shared-memory/L1 array asked for as shared memory; -1 driver
                                     default, -2 (default) the smallest that holds the resident CTAs */
     SPK_OPT_VERBOSE = 5,         /* 1: spk_cuda_choose_tracer prints its timings to stderr */
-    SPK_OPT_BUILD_MAX_LEAF = 6,  /* triangles per leaf of device-built BLAS (1..15, default 4) */
+    SPK_OPT_BUILD_MAX_LEAF = 6,  /* triangles per leaf of device-built BLAS (1..15, default 1: fastest to trace) */
     SPK_OPT_COST_ORDERED_STRIPS = 8, /* sorted megakernel: launch the strips of tiles in the order of their cost in the
                                     previous launch of the same view, longest first (default 1) */
     SPK_OPT_TRACE_SMEM_TOP = 7   /* ray-batch kernel: pairs of the hottest tree's top levels (the TLAS, else the first BLAS)

@@ -232,7 +232,7 @@ bool build_on_device(const SpkBvhDesc &d)
 // pair slots a mesh takes in the one pair array: what its host tree has, or the upper bound of a device build
 uint32_t mesh_pair_slots(const SpkMeshDesc &md)
 {
-    return build_on_device(md.blas) ? md.num_faces : (md.blas.num_nodes - 1) / 2;
+    return build_on_device(md.blas) ? md.num_faces : (md.blas.num_nodes - 1) / 2; // n - 1 pairs with one triangle per leaf
 }
 
 // ---- scene arena ----
@@ -1008,10 +1008,19 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         DeviceBuildResult res;
         cudaEvent_t e0 = ctx->ev0, e1 = ctx->ev1;
         SPK_CUDA_TRY(cudaEventRecord(e0, ctx->stream));
-        rc = device_build_lbvh(ctx, reinterpret_cast<const float *>(dev + mesh_off[m].vertices),
-                               reinterpret_cast<const uint32_t *>(dev + mesh_off[m].indices), nullptr, s->meshes[m].num_faces,
-                               ctx->opt_build_max_leaf, ctx->d_pairs, tree.pair_base, tree.leaf_base,
-                               reinterpret_cast<float4 *>(dev + off_tris) + size_t(tree.leaf_base) * 3, &res);
+        // one triangle per leaf traces fastest (tools/r2_lbvh_leaf_ab.py) but makes the deepest tree: a tree that does not
+        // fit the 32-entry traversal stack is rebuilt with larger leaves (each doubling takes about one level off)
+        for (uint32_t leaf = ctx->opt_build_max_leaf;; leaf = std::min(15u, leaf * 2u))
+        {
+            rc = device_build_lbvh(ctx, reinterpret_cast<const float *>(dev + mesh_off[m].vertices),
+                                   reinterpret_cast<const uint32_t *>(dev + mesh_off[m].indices), nullptr,
+                                   s->meshes[m].num_faces, leaf, ctx->d_pairs, tree.pair_base, tree.leaf_base,
+                                   reinterpret_cast<float4 *>(dev + off_tris) + size_t(tree.leaf_base) * 3, &res);
+            if (rc != SPK_ERR_UNSUPPORTED || leaf >= 15u)
+            {
+                break;
+            }
+        }
         if (rc != SPK_OK)
         {
             return rc;

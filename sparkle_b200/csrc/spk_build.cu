@@ -14,7 +14,8 @@
  * The same kernels build the TLAS from the instances' world boxes (max_leaf 1). spk_cuda_download_bvh hands any tree on the
  * device back in the bvh::v2 node layout + prim_ids, so the oracle traverses the SAME topology (tests/test_build_gpu.py:
  * closest hits bit-exact against the reference on the device-built tree, and equal to brute force).
- * An LBVH is a fast build, not a SAH-optimal one: the host builder (host/bvh_builder.cpp, binned SAH) stays the default for
+ * Leaves hold one triangle by default (SPK_OPT_BUILD_MAX_LEAF): an LBVH's leaves are spatially loose, larger ones cost more
+ * triangle tests than they save node visits. An LBVH is a fast build, not a SAH-optimal one: the host builder (host/bvh_builder.cpp, binned SAH) stays the default for
  * trees handed in by the caller; spk_cuda_get_build_info reports the SAH cost of either for comparison.
  * The reference's traversal stack holds 32 entries per level: a device-built tree deeper than 32 is refused.
  */

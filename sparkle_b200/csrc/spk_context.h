@@ -66,7 +66,9 @@ struct SpkContext
     size_t build_scratch_capacity = 0;
     uint32_t *build_ids = nullptr;
     float *d_tlas_boxes = nullptr; // world boxes of the primitives, in the scene arena
-    uint32_t opt_build_max_leaf = 4; // BLAS leaves of device-built trees (the TLAS always gets one primitive per leaf)
+    // BLAS leaves of device-built trees (the TLAS always gets one primitive per leaf). An LBVH's leaves are spatially
+    // loose: with 4 triangles per leaf soup-1M costs 13.7 triangle tests per ray against 2.1 with one, 1243 vs 1648 Mrays/s
+    uint32_t opt_build_max_leaf = 1;
     // where every tree of the current scene lives (spk_cuda_download_bvh, spk_cuda_update_instances, build reports)
     struct TreeInfo
     {
