@@ -319,6 +319,7 @@ typedef struct SpkPeerHandle {
     uint8_t bytes[SPK_PEER_HANDLE_BYTES];
 } SpkPeerHandle;
 typedef struct SpkGroup SpkGroup;
+/* Call once per group, before the handles are exchanged (it also clears the flags an earlier group of this context left). */
 int spk_cuda_group_export(SpkContext *ctx, SpkPeerHandle *out);
 int spk_cuda_group_create(SpkContext *ctx, uint32_t rank, uint32_t world, const SpkPeerHandle *handles, SpkGroup **out);
 int spk_cuda_group_create_local(SpkContext *const *ctxs, uint32_t n, SpkGroup **out);

@@ -579,7 +579,7 @@ int rebuild_tlas_on_device(SpkContext *ctx, const SpkPrimitiveDesc *prims, uint3
         float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
         if (pd.kind == SPK_PRIM_SPHERE)
         {
-            const float r = std::sqrt(pd.radius2);
+            const float r = std::sqrt(pd.radius2) * 1.000001f; // never inside the sphere by a rounding of the square root
             for (int a = 0; a < 3; a++)
             {
                 lo[a] = pd.fwd[4 * a + 3] - r;

@@ -332,6 +332,11 @@ int spk_cuda_group_export(SpkContext *ctx, SpkPeerHandle *out)
     h.height = ctx->height;
     h.host_id = host_identity();
     SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    // a new group counts its frames from 1 again: the flags a previous group of this context left behind are cleared HERE,
+    // before the handle can reach any peer (the exchange of the handles is the point every rank passes before it can
+    // create its group and signal anybody)
+    SPK_CUDA_TRY(cudaMemsetAsync(ctx->d_group_block, 0, sizeof(SyncBlock), ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     SPK_CUDA_TRY(cudaIpcGetMemHandle(&h.accum, ctx->d_accum));
     SPK_CUDA_TRY(cudaIpcGetMemHandle(&h.block, ctx->d_group_block));
     memset(out, 0, sizeof(*out));
