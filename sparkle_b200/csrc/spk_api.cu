@@ -6,6 +6,7 @@
 #include "spk_context.h"
 
 #include <cfloat>
+#include <chrono>
 #include <cstddef>
 #include <cmath>
 #include <cstdio>
@@ -654,6 +655,12 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     free_scene(ctx);
     int rc;
+    // SPK_OPT_VERBOSE: where the time of an upload goes (host clock)
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point t) {
+        return std::chrono::duration<double, std::milli>(now() - t).count();
+    };
+    const auto t_begin = now();
 
     // ---- validation (before any allocation) ----
     if ((s->num_meshes && !s->meshes) || (s->num_primitives && !s->primitives) || (s->num_materials && !s->materials) ||
@@ -769,6 +776,8 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
         }
     }
 
+    const double ms_validate = ms_since(t_begin);
+    const auto t_fill = now();
     // ---- lay the arena out (offsets only) ----
     ArenaPlan plan;
     // one spare pair so an all-leaf scene still has a valid (never dereferenced) pointer
@@ -990,9 +999,16 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     ctx->pair_capacity = uint32_t(total_pairs);
     ctx->instance_capacity = s->num_primitives;
 
+    const double ms_fill = ms_since(t_fill);
+    const auto t_copy = now();
     // ---- one copy, one synchronize (host pointers are borrowed for this call only) ----
     SPK_CUDA_TRY(cudaMemcpyAsync(dev, stage, plan.used, cudaMemcpyHostToDevice, ctx->stream));
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    if (ctx->opt_verbose)
+    {
+        fprintf(stderr, "[spk_cuda] upload_scene: validate %.2f ms, flatten + stage %.2f ms, copy %.1f MB %.2f ms\n", ms_validate,
+                ms_fill, plan.used / 1e6, ms_since(t_copy));
+    }
     ctx->d_pairs = reinterpret_cast<float4 *>(dev + off_pairs);
     ctx->d_instances = reinterpret_cast<DInstance *>(dev + off_inst);
     ctx->d_tlas_boxes = reinterpret_cast<float *>(dev + off_boxes);
