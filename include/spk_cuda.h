@@ -303,6 +303,18 @@ int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_ray
 /* Same with device-resident buffers (no copies); asynchronous on the context stream. */
 int spk_cuda_trace_closest_device(SpkContext *ctx, const void *d_rays, uint64_t num_rays, void *d_hits,
                                   uint32_t flags);
+/* spk_cuda_trace_closest for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). NO counterpart in the reference.
+ * Same host buffers, same hits bit for bit, but the staged rays, the hits and the kernel's ray ticket live in ONE static
+ * device array of the library (52 B x SPK_NOALLOC_MAX_RAYS + 256 B = 13.0 MiB, held by every GPU that loads the library
+ * until the process exits); the call makes no cudaMalloc / cudaFree / allocating library call. num_rays beyond
+ * SPK_NOALLOC_MAX_RAYS is refused with SPK_ERR_INVALID_ARGUMENT (split the batch, or use spk_cuda_trace_closest).
+ * `flags`: 0 or SPK_FLAG_EXACT_TRAVERSAL. Synchronous like spk_cuda_trace_closest. Every call on a GPU shares the array
+ * (whatever the context): calls that overlap on one GPU - two contexts on different streams or threads - race; serialise
+ * them. The array keeps the previous call's contents; what must start at zero (the ticket) is cleared by each call. */
+#define SPK_NOALLOC_MAX_RAYS 262144u
+int spk_cuda_trace_closest_noalloc(SpkContext *ctx, const SpkRay *rays, uint64_t num_rays, SpkHit *hits,
+                                   uint32_t flags);
 
 /* ---- multi-GPU behind the boundary (north_star (d)) ---------------------------------------------------
  * The scene is replicated, rank g of G renders samples {g, g+G, ...} (first_sample = g, sample_stride = G) into its own

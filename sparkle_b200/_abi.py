@@ -14,6 +14,7 @@ PRIM_MESH, PRIM_SPHERE = 0, 1
 MAT_PBR, MAT_DIELECTRIC = 0, 1
 FMT_RGBA8_UNORM, FMT_RGBA8_SRGB, FMT_RGBA16F, FMT_RGBA32F = 0, 1, 2, 3
 ACCUM_SUM, ACCUM_RUNNING_AVERAGE = 0, 1
+NOALLOC_MAX_RAYS = 262144  # SPK_NOALLOC_MAX_RAYS
 FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY, FLAG_AUTO_TRACER = 1, 2, 4, 8, 16
 FLAG_SPATIAL_DENOISE = 32
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
@@ -131,6 +132,7 @@ CUDA_SYMBOLS = {
     "spk_cuda_accum_sample_count": (C.c_int, [CtxP, u32p]),
     "spk_cuda_trace_closest": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
     "spk_cuda_trace_closest_device": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
+    "spk_cuda_trace_closest_noalloc": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
     "spk_cuda_group_export": (C.c_int, [CtxP, C.POINTER(PeerHandle)]),
     "spk_cuda_group_create": (C.c_int, [CtxP, u32, u32, C.POINTER(PeerHandle), C.POINTER(GroupP)]),
     "spk_cuda_group_create_local": (C.c_int, [C.POINTER(CtxP), u32, C.POINTER(GroupP)]),

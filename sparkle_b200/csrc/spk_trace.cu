@@ -11,6 +11,8 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
+#include <string>
 #include "spk_traverse.cuh"
 #include "spk_traverse_warp.cuh"
 
@@ -323,6 +325,131 @@ int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_ray
     SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
     SPK_CUDA_TRY(cudaMemcpyAsync(hits, ctx->d_hits, num_rays * sizeof(SpkHit), cudaMemcpyDeviceToHost, ctx->stream));
     SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return SPK_OK;
+}
+
+} // extern "C"
+
+// ---- spk_cuda_trace_closest_noalloc: the same ray batch call with NO allocation inside ------------------------------
+// spk_cuda_trace_closest stages the host batch in ctx->d_rays / ctx->d_hits (cudaMalloc'd on demand) and hands out rays
+// through a ticket counter. Here all three live in ONE file-scope device array that every GPU loading the library holds
+// until exit: [0, 256) the ticket (must be zero at launch: cleared on the stream before every launch), then the staged
+// rays (32 B each), then the hits (20 B each). The array keeps the previous call's rays and hits; they are overwritten
+// before they are read (rays by the copy-in, hits by the kernel: every ray writes its hit, misses included).
+namespace spk
+{
+namespace
+{
+constexpr uint64_t kNoAllocMaxRays = SPK_NOALLOC_MAX_RAYS;
+constexpr size_t kNoAllocTicketBytes = 256;
+constexpr size_t kNoAllocRaysAt = kNoAllocTicketBytes;
+constexpr size_t kNoAllocHitsAt = kNoAllocRaysAt + kNoAllocMaxRays * sizeof(SpkRay);
+constexpr size_t kNoAllocBytes = kNoAllocHitsAt + kNoAllocMaxRays * sizeof(SpkHit);
+static_assert(sizeof(SpkRay) == 32 && sizeof(SpkHit) == 20, "scratch layout follows the C ABI's ray and hit records");
+static_assert(kNoAllocHitsAt % 256 == 0, "hits start on a 256-byte boundary");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+unsigned char *g_noalloc_ptr[kNoAllocMaxDevices];    // device address of the array on each device, looked up once
+int g_noalloc_blocks_per_sm[2], g_noalloc_sms[kNoAllocMaxDevices];
+std::mutex g_noalloc_mutex;
+
+// the array's name in host code is a host-side stand-in: the kernel needs what cudaGetSymbolAddress returns on the device
+// that is current
+int noalloc_scratch(SpkContext *ctx, unsigned char **out)
+{
+    if (ctx->device < 0 || ctx->device >= kNoAllocMaxDevices)
+    {
+        set_error("spk_cuda_trace_closest_noalloc: device ordinal beyond 63");
+        return SPK_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[ctx->device])
+    {
+        void *p = nullptr;
+        SPK_CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        SPK_CUDA_TRY(cudaDeviceGetAttribute(&g_noalloc_sms[ctx->device], cudaDevAttrMultiProcessorCount, ctx->device));
+        g_noalloc_ptr[ctx->device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noalloc_ptr[ctx->device];
+    return SPK_OK;
+}
+
+template <bool CULL>
+int launch_noalloc(SpkContext *ctx, unsigned char *scratch, uint64_t n)
+{
+    auto kernel = trace_persistent_kernel<CULL, false, 6, false>;
+    int &blocks_per_sm = g_noalloc_blocks_per_sm[CULL ? 1 : 0];
+    if (blocks_per_sm == 0)
+    {
+        int b = 0;
+        SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kernel, kPersistWarps * 32, 0));
+        blocks_per_sm = b < 1 ? 1 : b;
+    }
+    const uint64_t want = (n + kPersistWarps * 32 - 1) / (kPersistWarps * 32);
+    const uint64_t resident = uint64_t(blocks_per_sm) * g_noalloc_sms[ctx->device];
+    const unsigned grid = unsigned(want < resident ? want : resident);
+    auto *ticket = reinterpret_cast<unsigned long long *>(scratch);
+    SPK_CUDA_TRY(cudaMemsetAsync(ticket, 0, kNoAllocTicketBytes, ctx->stream));
+    kernel<<<grid, kPersistWarps * 32, 0, ctx->stream>>>(ctx->scene, reinterpret_cast<const float4 *>(scratch + kNoAllocRaysAt), n,
+                                                        reinterpret_cast<float *>(scratch + kNoAllocHitsAt), ctx->d_counters,
+                                                        ticket, 0u);
+    SPK_CUDA_TRY(cudaGetLastError());
+    return SPK_OK;
+}
+} // namespace
+} // namespace spk
+
+extern "C"
+{
+int spk_cuda_trace_closest_noalloc(SpkContext *ctx, const SpkRay *rays, uint64_t num_rays, SpkHit *hits, uint32_t flags)
+{
+    if (!ctx || (num_rays && (!rays || !hits)))
+    {
+        set_error("spk_cuda_trace_closest_noalloc: null argument");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (flags & ~uint32_t(SPK_FLAG_EXACT_TRAVERSAL))
+    {
+        set_error("spk_cuda_trace_closest_noalloc: only SPK_FLAG_EXACT_TRAVERSAL is accepted");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (num_rays > kNoAllocMaxRays)
+    {
+        set_error("spk_cuda_trace_closest_noalloc: " + std::to_string(num_rays) + " rays exceed the static scratch's limit of " +
+                  std::to_string(kNoAllocMaxRays) + " (SPK_NOALLOC_MAX_RAYS); split the batch or use spk_cuda_trace_closest");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (!ctx->has_scene)
+    {
+        set_error("spk_cuda_trace_closest_noalloc: no scene uploaded");
+        return SPK_ERR_NO_SCENE;
+    }
+    if (num_rays == 0)
+    {
+        return SPK_OK;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    unsigned char *scratch = nullptr;
+    int rc = noalloc_scratch(ctx, &scratch);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    SPK_CUDA_TRY(cudaMemcpyAsync(scratch + kNoAllocRaysAt, rays, num_rays * sizeof(SpkRay), cudaMemcpyHostToDevice, ctx->stream));
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+    rc = (flags & SPK_FLAG_EXACT_TRAVERSAL) ? launch_noalloc<false>(ctx, scratch, num_rays)
+                                            : launch_noalloc<true>(ctx, scratch, num_rays);
+    if (rc != SPK_OK)
+    {
+        return rc;
+    }
+    SPK_CUDA_TRY(cudaEventRecord(ctx->ev1, ctx->stream));
+    SPK_CUDA_TRY(cudaMemcpyAsync(hits, scratch + kNoAllocHitsAt, num_rays * sizeof(SpkHit), cudaMemcpyDeviceToHost, ctx->stream));
+    SPK_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->stats.kernel_launches++;
+    ctx->stats.rays += num_rays;
     return SPK_OK;
 }
 

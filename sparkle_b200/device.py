@@ -97,6 +97,15 @@ class CudaContext:
         A.check(self.lib.spk_cuda_trace_closest(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data, flags))
         return hits
 
+    def trace_closest_noalloc(self, rays, flags=0, hits=None):
+        """trace_closest through the library's static device scratch: no allocation inside the call; at most
+        A.NOALLOC_MAX_RAYS rays. `hits`: optional preallocated HIT_DTYPE array to fill."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        if hits is None:
+            hits = np.empty(len(rays), HIT_DTYPE)
+        A.check(self.lib.spk_cuda_trace_closest_noalloc(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data, flags))
+        return hits
+
     def trace_closest_device(self, d_rays, n, d_hits, flags=0):
         A.check(self.lib.spk_cuda_trace_closest_device(self.handle, C.c_void_p(d_rays), n, C.c_void_p(d_hits), flags))
 
