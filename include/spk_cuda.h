@@ -359,6 +359,8 @@ typedef enum SpkOption {
     SPK_OPT_BUILD_MAX_LEAF = 6,  /* triangles per leaf of device-built BLAS (1..15, default 1: fastest to trace) */
     SPK_OPT_COST_ORDERED_STRIPS = 8, /* sorted megakernel: launch the strips of tiles in the order of their cost in the
                                     previous launch of the same view, longest first (default 1) */
+    SPK_OPT_WAVEFRONT_SORT = 9,  /* wavefront tracer: sort every ray queue by (Morton cell of the origin in the scene box,
+                                  * direction octant) before it is traced; value = bits per axis of the cell, 0 = off */
     SPK_OPT_TRACE_SMEM_TOP = 7   /* ray-batch kernel: pairs of the hottest tree's top levels (the TLAS, else the first BLAS)
                                     staged in shared memory: 0 (default, measured), 64, 128, 256, 512 */
 } SpkOption;

@@ -19,7 +19,7 @@ FLAG_EXACT_TRAVERSAL, FLAG_COUNTERS, FLAG_WAVEFRONT, FLAG_THREAD_PER_RAY, FLAG_A
 FLAG_SPATIAL_DENOISE = 32
 RESOLVE_LINEAR_F32, RESOLVE_TONEMAP_F16, RESOLVE_TONEMAP_SRGB8 = 0, 1, 2
 (OPT_MEGAKERNEL_FORM, OPT_WAVEFRONT_SLOTS, OPT_WAVEFRONT_CHUNK, OPT_TRACE_VOTE, OPT_SMEM_CARVEOUT,
- OPT_VERBOSE, OPT_BUILD_MAX_LEAF, OPT_TRACE_SMEM_TOP, OPT_COST_ORDERED_STRIPS) = range(9)
+ OPT_VERBOSE, OPT_BUILD_MAX_LEAF, OPT_TRACE_SMEM_TOP, OPT_COST_ORDERED_STRIPS, OPT_WAVEFRONT_SORT) = range(10)
 BVH_TLAS = 0xFFFFFFFF
 
 u32, i32, f32, u64 = C.c_uint32, C.c_int32, C.c_float, C.c_uint64

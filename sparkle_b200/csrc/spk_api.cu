@@ -471,6 +471,13 @@ int spk_cuda_set_option(SpkContext *ctx, uint32_t option, int64_t value)
         }
         ctx->opt_wf_chunk = uint32_t(value);
         return SPK_OK;
+    case SPK_OPT_WAVEFRONT_SORT:
+        if (value < 0 || value > 9)
+        {
+            return invalid("spk_cuda_set_option: wavefront sort key bits per axis must be in [0, 9]");
+        }
+        ctx->opt_wf_sort = uint32_t(value);
+        return SPK_OK;
     case SPK_OPT_TRACE_VOTE:
         if (value != 4 && value != 6 && value != 8 && value != 12 && value != 16)
         {

@@ -92,11 +92,13 @@ struct SpkContext
     // wavefront tracer: path-slot pool (spk_wavefront.cu)
     void *wf_block = nullptr;
     uint32_t wf_slots = 0;
+    size_t wf_bytes = 0;
     int mega_variant = 1084; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
     // explicit options (spk_cuda_set_option); nothing is read from the environment
     int opt_mega_form = 0;           // 0: use mega_variant
     uint32_t opt_wf_slots = 1u << 24; // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
     uint32_t opt_wf_chunk = 8;
+    uint32_t opt_wf_sort = 0; // wavefront ray sorting: bits per axis of the origin cell in the sort key (0 = off)
     int opt_vote = 6;
     int opt_trace_top = 0; // pairs of the hottest tree's top staged in shared memory by the ray-batch kernel (0 = off)
     int opt_carveout = -2;

@@ -21,6 +21,7 @@
 #include "spk_context.h"
 
 #include <cstdlib>
+#include <cub/device/device_radix_sort.cuh>
 #include "spk_shade.cuh"
 #include "spk_traverse.cuh"
 #include "spk_traverse_warp.cuh"
@@ -52,6 +53,7 @@ struct WfState
     float4 *thr;     // throughput.xyz
     uint32_t *queue[2];
     uint32_t *regen;
+    uint32_t *keys;  // sort key of every entry of the queue being filled (ray sorting on; else unused)
     WfCtrl *ctrl;
     uint32_t slots;
 };
@@ -61,7 +63,31 @@ struct WfArgs
     uint32_t width, height;
     uint32_t first_sample, sample_stride, max_bounce;
     float output_limit;
+    // ray sorting (SPK_OPT_WAVEFRONT_SORT): cells of the scene box, key_bits per axis; 0 = off
+    uint32_t key_bits;
+    float key_lo[3], key_scale[3];
 };
+
+// Sort key of a queued ray: Morton code of the origin's cell in the scene box, then the direction's octant. Rays that start
+// in the same cell and head into the same octant walk the same instances and the same side of their trees.
+__device__ __forceinline__ uint32_t spread3(uint32_t v) // 10 bits -> every third bit
+{
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t ray_sort_key(const WfArgs &a, V3 o, V3 d)
+{
+    const float top = (float)((1u << a.key_bits) - 1u);
+    const uint32_t cx = (uint32_t)fminf(fmaxf((o.x - a.key_lo[0]) * a.key_scale[0], 0.f), top);
+    const uint32_t cy = (uint32_t)fminf(fmaxf((o.y - a.key_lo[1]) * a.key_scale[1], 0.f), top);
+    const uint32_t cz = (uint32_t)fminf(fmaxf((o.z - a.key_lo[2]) * a.key_scale[2], 0.f), top);
+    const uint32_t cell = (spread3(cx) << 2) | (spread3(cy) << 1) | spread3(cz);
+    const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
+    return (cell << 3) | oct;
+}
 
 __global__ void wf_init_kernel(WfState st, unsigned long long total)
 {
@@ -90,6 +116,16 @@ __global__ void __launch_bounds__(kShadeThreads)
 {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     const WfCtrl c = *st.ctrl;
+    if (a.key_bits && k < st.slots)
+    {
+        // queue positions behind the last entry this iteration will have: largest key, so the sort leaves them at the end
+        const unsigned long long left = c.work_total - c.work_next;
+        const unsigned long long filled = c.n_queue[nxt] + (c.n_regen < left ? c.n_regen : left);
+        if (k >= filled)
+        {
+            st.keys[k] = 0xFFFFFFFFu;
+        }
+    }
     if (k >= c.n_regen)
     {
         return;
@@ -127,6 +163,10 @@ __global__ void __launch_bounds__(kShadeThreads)
     st.rng[slot] = make_uint4(rng.s0, rng.s1, rng.s2, rng.s3);
     st.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
     st.queue[nxt][c.n_queue[nxt] + k] = slot; // after the entries wf_shade appended; wf_advance adds the count
+    if (a.key_bits)
+    {
+        st.keys[c.n_queue[nxt] + k] = ray_sort_key(a, origin, dir);
+    }
 }
 
 __global__ void wf_advance_kernel(WfState st, uint32_t cur, unsigned long long *__restrict__ counters)
@@ -192,7 +232,7 @@ __global__ void __launch_bounds__(kExtendWarps * 32, SPK_WF_EXTEND_CTAS)
 
 // ---- shade: SamplePixel's loop body after Intersect (CPURenderer.cpp:259-369) for every traced slot
 #ifndef SPK_WF_SHADE_CTAS
-#define SPK_WF_SHADE_CTAS 1
+#define SPK_WF_SHADE_CTAS 3 // 80 registers: three CTAs per SM (the sort key would take it to 86 and two)
 #endif
 __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     wf_shade_kernel(const DScene sc, const WfArgs a, WfState st, uint32_t cur, float4 *__restrict__ accum)
@@ -240,6 +280,7 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     const uint32_t slot = s_sorted[tid];
 
     bool done = false, alive = slot != kEmptySlot;
+    uint32_t sort_key = 0;
     V3 color = mk(0.f, 0.f, 0.f);
     float valid = 1.f;
     uint32_t pixel = 0;
@@ -316,6 +357,10 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
                             make_float4(next_dir.x, next_dir.y, next_dir.z, __uint_as_float(bounce));
                         st.rng[slot] = make_uint4(rng.s0, rng.s1, rng.s2, rng.s3);
                         st.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.f);
+                        if (a.key_bits)
+                        {
+                            sort_key = ray_sort_key(a, origin, next_dir);
+                        }
                     }
                 }
             }
@@ -349,6 +394,10 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     if (alive && !done)
     {
         st.queue[nxt][base_c + __popc(m_cont & lt)] = slot;
+        if (a.key_bits)
+        {
+            st.keys[base_c + __popc(m_cont & lt)] = sort_key;
+        }
     }
     else if (alive)
     {
@@ -357,20 +406,39 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
 }
 } // namespace
 
-static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st)
+struct WfSort // ray sorting: a third queue buffer, the sorted keys and cub's scratch, behind the slot arrays
+{
+    uint32_t *queue_spare = nullptr, *keys_sorted = nullptr;
+    void *tmp = nullptr;
+    size_t tmp_bytes = 0;
+    int end_bit = 0;
+};
+
+static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st, WfSort &sort, uint32_t key_bits)
 {
     // one allocation, carved into 256-byte aligned arrays
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
     const size_t b_rays = al(size_t(slots) * 32), b_hit = al(size_t(slots) * 16), b_u32 = al(size_t(slots) * 4),
                  b_rng = al(size_t(slots) * 16), b_thr = al(size_t(slots) * 16);
-    const size_t total = b_rays + b_hit + b_u32 * 4 + b_rng + b_thr + 256;
-    if (ctx->wf_slots != slots)
+    size_t b_sort = 0;
+    sort.end_bit = int(3 * key_bits + 3);
+    if (key_bits)
+    {
+        SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, sort.tmp_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+                                                     (const uint32_t *)nullptr, (uint32_t *)nullptr, slots, 0, sort.end_bit,
+                                                     ctx->stream));
+        b_sort = 3 * b_u32 + al(sort.tmp_bytes);
+    }
+    const size_t total = b_rays + b_hit + b_u32 * 4 + b_rng + b_thr + 256 + b_sort;
+    if (ctx->wf_slots != slots || ctx->wf_bytes < total)
     {
         cudaFree(ctx->wf_block);
         ctx->wf_block = nullptr;
         ctx->wf_slots = 0;
+        ctx->wf_bytes = 0;
         SPK_CUDA_TRY(cudaMalloc(&ctx->wf_block, total));
         ctx->wf_slots = slots;
+        ctx->wf_bytes = total;
     }
     char *p = static_cast<char *>(ctx->wf_block);
     st.rays = reinterpret_cast<float4 *>(p);
@@ -390,12 +458,24 @@ static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st)
     st.regen = reinterpret_cast<uint32_t *>(p);
     p += b_u32;
     st.ctrl = reinterpret_cast<WfCtrl *>(p);
+    p += 256;
+    st.keys = nullptr;
+    if (key_bits)
+    {
+        st.keys = reinterpret_cast<uint32_t *>(p);
+        p += b_u32;
+        sort.keys_sorted = reinterpret_cast<uint32_t *>(p);
+        p += b_u32;
+        sort.queue_spare = reinterpret_cast<uint32_t *>(p);
+        p += b_u32;
+        sort.tmp = p;
+    }
     st.slots = slots;
     return SPK_OK;
 }
 
 template <bool CULL, bool COUNT>
-static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t sample_count)
+static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &sort, uint32_t sample_count)
 {
 #ifndef SPK_WF_REFILL
 #define SPK_WF_REFILL 8
@@ -425,16 +505,36 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t 
     uint32_t chunk = uint32_t(least < 4096ull ? least : 4096ull);
     const uint32_t chunk_next = ctx->opt_wf_chunk;
     uint32_t cur = 0;
+    // ray sorting: three queue buffers rotate. The queue an iteration fills is sorted by ray key into the spare buffer,
+    // which wf_extend and the next wf_shade read; the counts in the control block stay indexed by parity.
+    uint32_t *q_cur = st.queue[0], *q_nxt = st.queue[1], *q_spare = sort.queue_spare;
+    uint32_t sort_items = slots; // entries the sort covers: all slots until the work runs out, then what is left
     WfCtrl h{};
     for (;; chunk = chunk_next)
     {
         for (uint32_t it = 0; it < chunk; it++)
         {
+            st.queue[cur] = q_cur;
+            st.queue[cur ^ 1u] = q_nxt;
             wf_shade_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur, ctx->d_accum);
             wf_regen_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->camera, a, st, cur ^ 1u);
             wf_advance_kernel<<<1, 1, 0, s>>>(st, cur, ctx->d_counters);
-            extend<<<extend_blocks, kExtendWarps * 32, 0, s>>>(ctx->scene, st, cur ^ 1u, ctx->d_counters);
             ctx->stats.kernel_launches += 4;
+            if (a.key_bits)
+            {
+                size_t bytes = sort.tmp_bytes;
+                SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort.tmp, bytes, (const uint32_t *)st.keys, sort.keys_sorted,
+                                                             (const uint32_t *)q_nxt, q_spare, sort_items, 0, sort.end_bit, s));
+                uint32_t *t = q_nxt;
+                q_nxt = q_spare;
+                q_spare = t;
+                st.queue[cur ^ 1u] = q_nxt;
+            }
+            extend<<<extend_blocks, kExtendWarps * 32, 0, s>>>(ctx->scene, st, cur ^ 1u, ctx->d_counters);
+            // next iteration: the traced queue is read, the one just consumed is refilled
+            uint32_t *t = q_cur;
+            q_cur = q_nxt;
+            q_nxt = t;
             cur ^= 1u;
         }
         SPK_CUDA_TRY(cudaGetLastError());
@@ -443,6 +543,10 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, const WfState &st, uint32_t 
         if (h.work_next >= h.work_total && h.n_queue[cur] == 0)
         {
             break;
+        }
+        if (h.work_next >= h.work_total && h.n_queue[cur] < sort_items)
+        {
+            sort_items = h.n_queue[cur]; // no new paths: the queue only shrinks from here
         }
     }
     return SPK_OK;
@@ -479,19 +583,32 @@ int launch_render_wavefront(SpkContext *ctx, const SpkRenderParams *p)
         slots = uint32_t(total);
     }
     slots = (slots + 255u) & ~255u;
+    // ray sorting: cells of the scene box (the TLAS root's bounds)
+    a.key_bits = ctx->opt_wf_sort;
+    for (int k = 0; k < 3; k++)
+    {
+        const float lo = ctx->tlas_tree.root_bounds[k], hi = ctx->tlas_tree.root_bounds[3 + k];
+        a.key_lo[k] = lo;
+        a.key_scale[k] = hi > lo ? float(1u << a.key_bits) / (hi - lo) : 0.f;
+    }
+    if (ctx->scene.num_instances == 0)
+    {
+        a.key_bits = 0;
+    }
     WfState st;
-    int rc = wf_reserve(ctx, slots, st);
+    WfSort sort;
+    int rc = wf_reserve(ctx, slots, st, sort, a.key_bits);
     if (rc != SPK_OK)
     {
         return rc;
     }
     const bool exact = p->flags & SPK_FLAG_EXACT_TRAVERSAL, count = p->flags & SPK_FLAG_COUNTERS;
     if (exact && count)
-        return wf_run<false, true>(ctx, a, st, p->sample_count);
+        return wf_run<false, true>(ctx, a, st, sort, p->sample_count);
     if (exact)
-        return wf_run<false, false>(ctx, a, st, p->sample_count);
+        return wf_run<false, false>(ctx, a, st, sort, p->sample_count);
     if (count)
-        return wf_run<true, true>(ctx, a, st, p->sample_count);
-    return wf_run<true, false>(ctx, a, st, p->sample_count);
+        return wf_run<true, true>(ctx, a, st, sort, p->sample_count);
+    return wf_run<true, false>(ctx, a, st, sort, p->sample_count);
 }
 } // namespace spk
