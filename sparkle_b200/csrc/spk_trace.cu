@@ -61,6 +61,9 @@ __global__ void __launch_bounds__(kTraceThreads)
 
 // ---- persistent, warp-converged form (spk_traverse_warp.cuh): the default for ray batches ----
 constexpr int kPersistWarps = 4;
+#ifndef SPK_TRACE_REFILL
+#define SPK_TRACE_REFILL 16
+#endif
 
 template <bool CULL, bool COUNT, int VOTE, bool TOP = false>
 __global__ void __launch_bounds__(kPersistWarps * 32)
@@ -85,9 +88,7 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
         o[3] = __uint_as_float(prim);
         o[4] = __uint_as_float(best.face);
     };
-    warp_trace_loop<CULL, COUNT, 16, VOTE, TOP>(
-        sc, n, next_ray, s_lane_words, cnt,
-        [&](unsigned long long id, V3 &o, V3 &d) {
+    auto fetch = [&](unsigned long long id, V3 &o, V3 &d) {
             if (sc.num_instances == 0)
             {
                 Hit miss{SPK_FLT_MAX, 0.f, 0.f, SPK_INVALID_ID, SPK_INVALID_ID}; // empty scene: every ray misses
@@ -98,8 +99,17 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
             o = mk(ro.x, ro.y, ro.z);
             d = mk(rd.x, rd.y, rd.z);
             return true;
-        },
-        write_hit, top);
+        };
+#if SPK_POSTPONE_LEAF
+    if (!TOP)
+    {
+        warp_trace_loop_postponed<CULL, COUNT, SPK_TRACE_REFILL, VOTE>(sc, n, next_ray, s_lane_words, cnt, fetch, write_hit);
+    }
+    else
+#endif
+    {
+        warp_trace_loop<CULL, COUNT, SPK_TRACE_REFILL, VOTE, TOP>(sc, n, next_ray, s_lane_words, cnt, fetch, write_hit, top);
+    }
     if (COUNT)
     {
         const unsigned lane = threadIdx.x & 31u;

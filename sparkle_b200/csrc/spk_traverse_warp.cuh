@@ -22,6 +22,10 @@
 #pragma once
 #include "spk_traverse.cuh"
 
+#ifndef SPK_POSTPONE_LEAF
+#define SPK_POSTPONE_LEAF 0
+#endif
+
 namespace spk
 {
 constexpr uint32_t kSentinel = 0xFFFFFFFFu; // stack marker: "leave the instance, back to the TLAS"
@@ -270,6 +274,273 @@ __device__ __forceinline__ bool lane_tlas_step(const DScene &sc, LaneState &s, L
     stack.push(s.sp, kSentinel);
     s.top = __ldg(&in->root);
     return true;
+}
+
+// ---- postponed-leaf form of the lane state machine (SPK_POSTPONE_LEAF) ----------------------------------------------
+// A lane that reaches a triangle leaf does not wait for the warp's next triangle step: it parks the leaf in `pend` and goes
+// on with the inner nodes on its stack (speculative traversal, Aila & Laine 2009); only a second leaf, the end of the
+// instance (the sentinel) or an empty stack make it wait. A triangle step then serves EVERY lane that has a parked leaf,
+// waiting or not. Leaves are still tested in the order the traversal reaches them (pend before top), and a bound that is
+// shortened later only ever skips nodes that cannot hold a closer hit, so the closest hit is the same, bit for bit; the
+// culled form visits a few more nodes than the in-order loop because its bound lags by one leaf.
+constexpr uint32_t kEmptyStack = 0xFFFFFFFDu; // `top` of a lane whose stack ran empty (low nibble != 0: not an inner node)
+enum LaneMode : int
+{
+    kLaneIdle = 0,
+    kLaneInner = 1,
+    kLaneWaitTri = 2,
+    kLaneWaitTlas = 3
+};
+
+__device__ __forceinline__ void lane_leave_instance(LaneState &s, LaneStack &stack)
+{
+    s.inst = SPK_INVALID_ID;
+    s.lo = s.wo;
+    s.ld = s.wd;
+    const float *w = reinterpret_cast<const float *>(stack.sm) + kSmemStack * 32;
+    s.sr.ix = w[0];
+    s.sr.iy = w[32];
+    s.sr.iz = w[64];
+    s.sr.ox = w[96];
+    s.sr.oy = w[128];
+    s.sr.oz = w[160];
+    s.sr.nx = signbit(s.wd.x);
+    s.sr.ny = signbit(s.wd.y);
+    s.sr.nz = signbit(s.wd.z);
+}
+
+__device__ __forceinline__ uint32_t lane_next(LaneState &s, LaneStack &stack)
+{
+    return s.sp ? stack.pop(s.sp) : kEmptyStack;
+}
+
+// bring a lane to the next thing it can do: park a triangle leaf, leave an instance, ... until `top` is an inner node or the
+// lane has to wait
+__device__ __forceinline__ int lane_settle(LaneState &s, LaneStack &stack, uint32_t &pend)
+{
+    for (;;)
+    {
+        const uint32_t top = s.top;
+        if ((top & 15u) == 0u)
+        {
+            return kLaneInner;
+        }
+        if (top == kEmptyStack)
+        {
+            return pend ? kLaneWaitTri : kLaneIdle;
+        }
+        if (top == kSentinel)
+        {
+            if (pend)
+            {
+                return kLaneWaitTri; // the parked leaf belongs to this instance: test it before the ray goes back
+            }
+            lane_leave_instance(s, stack);
+        }
+        else if (s.inst != SPK_INVALID_ID)
+        {
+            if (pend)
+            {
+                return kLaneWaitTri;
+            }
+            pend = top;
+        }
+        else
+        {
+            return kLaneWaitTlas;
+        }
+        s.top = lane_next(s, stack);
+    }
+}
+
+template <bool CULL, bool COUNT>
+__device__ __forceinline__ void lane_inner_step_np(const float4 *__restrict__ pairs, LaneState &s, LaneStack &stack,
+                                                   TraceCounters &cnt)
+{
+    const float4 *p = pairs + size_t(s.top >> 4) * 4;
+    float4 l0, l1, r0, r1;
+    ldg256(p, l0, l1);
+    ldg256(p + 2, r0, r1);
+    if (COUNT)
+    {
+        cnt.node_visits++;
+    }
+    bool hl, hr;
+    float tl = slab(s.sr, l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, hl);
+    float tr = slab(s.sr, r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, hr);
+    if (CULL)
+    {
+        float bound = s.best.t + (s.best.t * 2.44140625e-4f + s.slack_abs);
+        hl = hl && tl <= bound;
+        hr = hr && tr <= bound;
+    }
+    const uint32_t li = __float_as_uint(l1.z), ri = __float_as_uint(r1.z);
+    if (hl)
+    {
+        uint32_t near_i = li;
+        if (hr)
+        {
+            uint32_t far_i = ri;
+            if (tl > tr)
+            {
+                near_i = ri;
+                far_i = li;
+            }
+            stack.push(s.sp, far_i);
+        }
+        s.top = near_i;
+    }
+    else
+    {
+        s.top = hr ? ri : lane_next(s, stack);
+    }
+}
+
+// one triangle of the parked leaf
+template <bool COUNT>
+__device__ __forceinline__ void lane_pend_step(const DScene &sc, LaneState &s, uint32_t &pend, TraceCounters &cnt)
+{
+    const uint32_t first = pend >> 4, count = pend & 15u;
+    const float fwd_row0[4] = {s.f0, s.f1, s.f2, s.f3};
+    if (COUNT)
+    {
+        cnt.tri_tests++;
+    }
+    intersect_triangle(sc.tris + size_t(first) * 3, s.lo, s.ld, s.wo, s.wd, fwd_row0, s.inst, s.best);
+    pend = count > 1u ? (((first + 1u) << 4) | (count - 1u)) : 0u;
+}
+
+// TLAS leaf in `top` (lane_tlas_step without the pop)
+template <bool COUNT>
+__device__ __forceinline__ void lane_tlas_step_np(const DScene &sc, LaneState &s, LaneStack &stack, TraceCounters &cnt)
+{
+    const uint32_t first = s.top >> 4, count = s.top & 15u;
+    if (count > 1u)
+    {
+        stack.push(s.sp, ((first + 1u) << 4) | (count - 1u));
+    }
+    const DInstance *__restrict__ in = sc.instances + first;
+    if (__ldg(&in->kind) == 1u)
+    {
+        if (COUNT)
+        {
+            cnt.sphere_tests++;
+        }
+        intersect_sphere(in, s.wo, s.wd, first, s.best);
+        s.top = lane_next(s, stack);
+        return;
+    }
+    if (COUNT)
+    {
+        cnt.inst_visits++;
+    }
+    float inv[12];
+    const float4 *m = reinterpret_cast<const float4 *>(in);
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        float4 a = __ldg(m + k);
+        inv[4 * k] = a.x;
+        inv[4 * k + 1] = a.y;
+        inv[4 * k + 2] = a.z;
+        inv[4 * k + 3] = a.w;
+    }
+    float4 f = __ldg(m + 3);
+    s.f0 = f.x;
+    s.f1 = f.y;
+    s.f2 = f.z;
+    s.f3 = f.w;
+    s.lo = xform_point(inv, s.wo);
+    s.ld = xform_dir(inv, s.wd);
+    s.sr = make_slab_ray(s.lo, s.ld);
+    s.inst = first;
+    stack.push(s.sp, kSentinel);
+    s.top = __ldg(&in->root);
+}
+
+template <bool CULL, bool COUNT, int REFILL, int VOTE, typename Fetch, typename Store>
+__device__ __forceinline__ void warp_trace_loop_postponed(const DScene &sc, unsigned long long n, unsigned long long *cursor,
+                                                          uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch,
+                                                          Store &&store)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    LaneStack stack;
+    stack.sm = s_lane_words + (threadIdx.x >> 5) * (kLaneSmemWords * 32) + lane;
+    LaneState s;
+    s.top = kEmptyStack;
+    s.inst = SPK_INVALID_ID;
+    s.sp = 0;
+    uint32_t pend = 0;
+    int mode = kLaneIdle;
+    unsigned long long ray_id = ~0ull;
+    bool exhausted = false;
+    const float4 *__restrict__ pairs = sc.pairs;
+    for (;;)
+    {
+        const unsigned idle = __ballot_sync(0xffffffffu, mode == kLaneIdle);
+        if (idle == 0xffffffffu && exhausted)
+        {
+            break;
+        }
+        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xffffffffu))
+        {
+            unsigned long long base = 0;
+            const int leader = __ffs(idle) - 1;
+            if ((int)lane == leader)
+            {
+                base = atomicAdd(cursor, (unsigned long long)__popc(idle));
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (mode == kLaneIdle)
+            {
+                unsigned long long id = base + __popc(idle & lt_mask);
+                V3 o, d;
+                if (id < n && fetch(id, o, d))
+                {
+                    lane_begin<CULL>(sc, s, stack, o, d);
+                    ray_id = id;
+                    pend = 0;
+                    mode = lane_settle(s, stack, pend);
+                }
+            }
+            exhausted = base + __popc(idle) >= n;
+        }
+        const int c_inner = __popc(__ballot_sync(0xffffffffu, mode == kLaneInner));
+        const int c_tri = __popc(__ballot_sync(0xffffffffu, mode == kLaneWaitTri));
+        const int c_tlas = __popc(__ballot_sync(0xffffffffu, mode == kLaneWaitTlas));
+        const bool run_tri = c_tri >= VOTE || (c_inner == 0 && c_tri > 0 && c_tri >= c_tlas);
+        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (c_inner == 0 && c_tlas > 0));
+        if (run_tri)
+        {
+            if (pend) // waiting lanes and lanes that are still walking with a parked leaf
+            {
+                lane_pend_step<COUNT>(sc, s, pend, cnt);
+                if (mode == kLaneWaitTri)
+                {
+                    mode = lane_settle(s, stack, pend);
+                }
+            }
+        }
+        else if (run_tlas)
+        {
+            if (mode == kLaneWaitTlas)
+            {
+                lane_tlas_step_np<COUNT>(sc, s, stack, cnt);
+                mode = lane_settle(s, stack, pend);
+            }
+        }
+        else if (mode == kLaneInner)
+        {
+            lane_inner_step_np<CULL, COUNT>(pairs, s, stack, cnt);
+            mode = lane_settle(s, stack, pend);
+        }
+        if (mode == kLaneIdle && ray_id != ~0ull)
+        {
+            store(ray_id, s.best);
+            ray_id = ~0ull;
+        }
+    }
 }
 
 /*

@@ -6,8 +6,8 @@
  * megakernel's; only the ORDER in which samples are added to a pixel differs (vector float atomics), i.e. float
  * association of the sum (~1e-7 relative). SPK_ACCUM_SUM only.
  *
- * A pool of P path slots lives in HBM/L2 (84 B per slot: ray 32 B carrying pixel + bounce in its pad words, hit 20 B,
- * rng 16 B, throughput 16 B). One iteration = four launches, no host round trip (counts live in a device control block):
+ * A pool of P path slots lives in HBM (one 96-byte record per slot, see WfState). One iteration = four launches, no host
+ * round trip (counts live in a device control block):
  *   wf_shade    one thread per traced slot. The CTA first sorts its 256 slots by material class in shared memory
  *               (miss / sphere|mesh x pbr|dielectric x textured x emissive), so a warp shades like with like.
  *               Continuing paths are appended to the next ray queue, finished ones to the regen list
@@ -33,6 +33,7 @@ namespace
 constexpr int kShadeThreads = 256;
 constexpr int kExtendWarps = 4;
 constexpr uint32_t kEmptySlot = 0xFFFFFFFFu;
+constexpr size_t kRec = 6; // float4 per slot record
 
 struct WfCtrl
 {
@@ -46,11 +47,13 @@ struct WfCtrl
 
 struct WfState
 {
-    float4 *rays;    // 2 per slot: {origin.xyz, pixel bits}, {direction.xyz, bounce bits}
-    float4 *hit;     // {t, u, v, instance slot bits}
-    uint32_t *face;
-    uint4 *rng;
-    float4 *thr;     // throughput.xyz
+    // One 96-byte record per slot, three 32-byte sectors that are always read and written whole (the slot order of a queue
+    // is close to random after a few bounces: with one array per field every 4- or 16-byte access cost a sector of its own
+    // and partial sector writes cost a fill on top, 586 B of DRAM traffic per shaded slot):
+    //   [0] {origin.xyz, pixel bits} [1] {direction.xyz, bounce bits}      written by regen / shade, read by extend / shade
+    //   [2] {t, u, v, instance slot bits} [3] {face bits, -, -, -}         written by extend, read by shade
+    //   [4] rng state [5] {throughput.xyz, -}                              written by regen / shade, read by shade
+    float4 *rec;
     uint32_t *queue[2];
     uint32_t *regen;
     uint32_t *keys;  // sort key of every entry of the queue being filled (ray sorting on; else unused)
@@ -95,7 +98,7 @@ __global__ void wf_init_kernel(WfState st, unsigned long long total)
     if (k < st.slots)
     {
         st.regen[k] = k;
-        st.rays[2 * size_t(k)].w = __uint_as_float(kEmptySlot);
+        st.rec[kRec * size_t(k)].w = __uint_as_float(kEmptySlot);
     }
     if (k == 0)
     {
@@ -114,58 +117,67 @@ __global__ void wf_init_kernel(WfState st, unsigned long long total)
 __global__ void __launch_bounds__(kShadeThreads)
     wf_regen_kernel(const DCamera cam, const WfArgs a, WfState st, uint32_t nxt)
 {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     const WfCtrl c = *st.ctrl;
-    if (a.key_bits && k < st.slots)
-    {
-        // queue positions behind the last entry this iteration will have: largest key, so the sort leaves them at the end
-        const unsigned long long left = c.work_total - c.work_next;
-        const unsigned long long filled = c.n_queue[nxt] + (c.n_regen < left ? c.n_regen : left);
-        if (k >= filled)
-        {
-            st.keys[k] = 0xFFFFFFFFu;
-        }
-    }
-    if (k >= c.n_regen)
-    {
-        return;
-    }
-    const uint32_t slot = st.regen[k];
-    const unsigned long long w = c.work_next + k;
-    if (w >= c.work_total)
-    {
-        st.rays[2 * size_t(slot)].w = __uint_as_float(kEmptySlot);
-        return;
-    }
+    const unsigned long long left = c.work_total - c.work_next;
+    const uint32_t gen = uint32_t(c.n_regen < left ? c.n_regen : left); // slots that get a new path
     const uint32_t npix = a.width * a.height;
-    const uint32_t s = uint32_t(w / npix), p = uint32_t(w % npix);
-    const uint32_t i = p % a.width, j = p / a.width;
+    const uint32_t s0 = uint32_t(c.work_next / npix), p0 = uint32_t(c.work_next % npix);
     const float pw = 1.f / (float)(a.width - 1), ph = 1.f / (float)(a.height - 1);
-    const uint32_t frame_seed = a.first_sample + s * a.sample_stride; // CPURenderer.cpp:442-443, unsigned wrap
-    Rng rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
-    float u = ((float)i + rng_unit(rng)) * pw;
-    float v = ((float)j + rng_unit(rng)) * ph;
-    float dx, dy;
-    unit_disk(rng, dx, dy);
-    dx = dx * cam.aperture_radius;
-    dy = dy * cam.aperture_radius;
     const V3 cpos = mk(cam.position[0], cam.position[1], cam.position[2]);
     const V3 cup = mk(cam.up[0], cam.up[1], cam.up[2]);
     const V3 cright = mk(cam.right[0], cam.right[1], cam.right[2]);
     const V3 max_u = mk(cam.max_u[0], cam.max_u[1], cam.max_u[2]);
     const V3 max_v = mk(cam.max_v[0], cam.max_v[1], cam.max_v[2]);
     const V3 lower_left = mk(cam.lower_left[0], cam.lower_left[1], cam.lower_left[2]);
-    V3 origin = cpos + (dx * cright + dy * cup);
-    V3 target = lower_left + u * max_u + v * max_v;
-    V3 dir = normalized(target - origin);
-    st.rays[2 * size_t(slot)] = make_float4(origin.x, origin.y, origin.z, __uint_as_float(p));
-    st.rays[2 * size_t(slot) + 1] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(0u));
-    st.rng[slot] = make_uint4(rng.s0, rng.s1, rng.s2, rng.s3);
-    st.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-    st.queue[nxt][c.n_queue[nxt] + k] = slot; // after the entries wf_shade appended; wf_advance adds the count
+    // a fixed grid strides over the list (its length is only known on the device)
+    const uint32_t stride = gridDim.x * blockDim.x;
     if (a.key_bits)
     {
-        st.keys[c.n_queue[nxt] + k] = ray_sort_key(a, origin, dir);
+        // queue positions behind the last entry this iteration will have: largest key, so the sort leaves them at the end
+        for (uint32_t k = c.n_queue[nxt] + gen + blockIdx.x * blockDim.x + threadIdx.x; k < st.slots; k += stride)
+        {
+            st.keys[k] = 0xFFFFFFFFu;
+        }
+    }
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < c.n_regen; k += stride)
+    {
+        const uint32_t slot = st.regen[k];
+        if (k >= gen)
+        {
+            st.rec[kRec * size_t(slot)].w = __uint_as_float(kEmptySlot); // no work left for this slot
+            continue;
+        }
+        // work item w = work_next + k = sample * W*H + pixel, without a 64-bit division per path
+        uint32_t s = s0;
+        unsigned long long p64 = (unsigned long long)p0 + k;
+        while (p64 >= npix)
+        {
+            p64 -= npix;
+            s++;
+        }
+        const uint32_t p = uint32_t(p64);
+        const uint32_t i = p % a.width, j = p / a.width;
+        const uint32_t frame_seed = a.first_sample + s * a.sample_stride; // CPURenderer.cpp:442-443, unsigned wrap
+        Rng rng = rng_seed(j * a.width + i + frame_seed * a.width * a.height);
+        float u = ((float)i + rng_unit(rng)) * pw;
+        float v = ((float)j + rng_unit(rng)) * ph;
+        float dx, dy;
+        unit_disk(rng, dx, dy);
+        dx = dx * cam.aperture_radius;
+        dy = dy * cam.aperture_radius;
+        V3 origin = cpos + (dx * cright + dy * cup);
+        V3 target = lower_left + u * max_u + v * max_v;
+        V3 dir = normalized(target - origin);
+        float4 *r = st.rec + kRec * size_t(slot);
+        r[0] = make_float4(origin.x, origin.y, origin.z, __uint_as_float(p));
+        r[1] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(0u));
+        r[4] = make_float4(__uint_as_float(rng.s0), __uint_as_float(rng.s1), __uint_as_float(rng.s2), __uint_as_float(rng.s3));
+        r[5] = make_float4(1.f, 1.f, 1.f, 0.f);
+        st.queue[nxt][c.n_queue[nxt] + k] = slot; // after the entries wf_shade appended; wf_advance adds the count
+        if (a.key_bits)
+        {
+            st.keys[c.n_queue[nxt] + k] = ray_sort_key(a, origin, dir);
+        }
     }
 }
 
@@ -195,24 +207,29 @@ __global__ void __launch_bounds__(kExtendWarps * 32, SPK_WF_EXTEND_CTAS)
 {
     __shared__ uint32_t s_lane_words[kExtendWarps * kLaneSmemWords * 32];
     const uint32_t *__restrict__ queue = st.queue[q];
-    const float4 *__restrict__ rays = st.rays;
+    const float4 *rec = st.rec;
     TraceCounters cnt{0, 0, 0, 0};
 #ifndef SPK_WF_VOTE
 #define SPK_WF_VOTE 8
 #endif
+#if SPK_POSTPONE_LEAF
+    warp_trace_loop_postponed<CULL, COUNT, REFILL, SPK_WF_VOTE>(
+#else
     warp_trace_loop<CULL, COUNT, REFILL, SPK_WF_VOTE>(
+#endif
         sc, st.ctrl->n_queue[q], &st.ctrl->next_ray, s_lane_words, cnt,
         [&](unsigned long long id, V3 &o, V3 &d) {
             const uint32_t slot = __ldg(queue + id);
-            float4 ro = rays[2 * size_t(slot)], rd = rays[2 * size_t(slot) + 1];
+            float4 ro = rec[kRec * size_t(slot)], rd = rec[kRec * size_t(slot) + 1];
             o = mk(ro.x, ro.y, ro.z);
             d = mk(rd.x, rd.y, rd.z);
             return true;
         },
         [&](unsigned long long id, const Hit &best) {
             const uint32_t slot = __ldg(queue + id);
-            st.hit[slot] = make_float4(best.t, best.u, best.v, __uint_as_float(best.inst));
-            st.face[slot] = best.face;
+            float4 *r = st.rec + kRec * size_t(slot) + 2;
+            r[0] = make_float4(best.t, best.u, best.v, __uint_as_float(best.inst));
+            r[1] = make_float4(__uint_as_float(best.face), 0.f, 0.f, 0.f); // the whole sector: no fill for a partial write
         });
     if (COUNT)
     {
@@ -238,7 +255,9 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     wf_shade_kernel(const DScene sc, const WfArgs a, WfState st, uint32_t cur, float4 *__restrict__ accum)
 {
     __shared__ uint32_t s_bin[32];
-    __shared__ uint32_t s_sorted[kShadeThreads];
+    // the slot state travels through shared memory to the thread that shades it: [word][sorted position]
+    constexpr int kStateWords = 22; // slot, ray 8, hit 4, face, throughput 4 (w unused), rng 4
+    __shared__ uint32_t s_state[kStateWords * kShadeThreads];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t k = blockIdx.x * kShadeThreads + tid;
     const uint32_t n = st.ctrl->n_queue[cur];
@@ -246,17 +265,30 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     {
         return; // whole CTA beyond the queue
     }
-    // -- CTA-local counting sort of this CTA's slots by material class
+    // -- every thread fetches ALL the state of the slot at its queue position in one round of independent loads (the class
+    //    used to be fetched first, the rest after the sort and the rng after the emissive test: three dependent trips to
+    //    HBM per path), then the CTA counting-sorts the slots by material class and hands the state over in shared memory
     if (tid < 32)
     {
         s_bin[tid] = 0;
     }
     __syncthreads();
     uint32_t my = kEmptySlot, key = 31u, pos = 0;
+    float4 q_ro = make_float4(0.f, 0.f, 0.f, 0.f), q_rd = q_ro, q_h = q_ro, q_t = q_ro;
+    uint4 q_rng = make_uint4(0u, 0u, 0u, 0u);
+    uint32_t q_face = 0;
     if (k < n)
     {
         my = st.queue[cur][k];
-        key = shade_class(sc, __float_as_uint(st.hit[my].w));
+        const float4 *r = st.rec + kRec * size_t(my);
+        q_ro = r[0];
+        q_rd = r[1];
+        q_h = r[2];
+        q_face = __float_as_uint(r[3].x);
+        const float4 g = r[4];
+        q_rng = make_uint4(__float_as_uint(g.x), __float_as_uint(g.y), __float_as_uint(g.z), __float_as_uint(g.w));
+        q_t = r[5];
+        key = shade_class(sc, __float_as_uint(q_h.w));
     }
     pos = atomicAdd(&s_bin[key], 1u);
     __syncthreads();
@@ -275,9 +307,33 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
         s_bin[tid] = incl - c; // exclusive start of the class
     }
     __syncthreads();
-    s_sorted[s_bin[key] + pos] = my;
+    {
+        uint32_t *o = s_state + s_bin[key] + pos;
+        o[0 * kShadeThreads] = my;
+        o[1 * kShadeThreads] = __float_as_uint(q_ro.x);
+        o[2 * kShadeThreads] = __float_as_uint(q_ro.y);
+        o[3 * kShadeThreads] = __float_as_uint(q_ro.z);
+        o[4 * kShadeThreads] = __float_as_uint(q_ro.w);
+        o[5 * kShadeThreads] = __float_as_uint(q_rd.x);
+        o[6 * kShadeThreads] = __float_as_uint(q_rd.y);
+        o[7 * kShadeThreads] = __float_as_uint(q_rd.z);
+        o[8 * kShadeThreads] = __float_as_uint(q_rd.w);
+        o[9 * kShadeThreads] = __float_as_uint(q_h.x);
+        o[10 * kShadeThreads] = __float_as_uint(q_h.y);
+        o[11 * kShadeThreads] = __float_as_uint(q_h.z);
+        o[12 * kShadeThreads] = __float_as_uint(q_h.w);
+        o[13 * kShadeThreads] = q_face;
+        o[14 * kShadeThreads] = __float_as_uint(q_t.x);
+        o[15 * kShadeThreads] = __float_as_uint(q_t.y);
+        o[16 * kShadeThreads] = __float_as_uint(q_t.z);
+        o[17 * kShadeThreads] = q_rng.x;
+        o[18 * kShadeThreads] = q_rng.y;
+        o[19 * kShadeThreads] = q_rng.z;
+        o[20 * kShadeThreads] = q_rng.w;
+    }
     __syncthreads();
-    const uint32_t slot = s_sorted[tid];
+    const uint32_t *in = s_state + tid;
+    const uint32_t slot = in[0];
 
     bool done = false, alive = slot != kEmptySlot;
     uint32_t sort_key = 0;
@@ -286,18 +342,20 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     uint32_t pixel = 0;
     if (alive)
     {
-        const float4 ro = st.rays[2 * size_t(slot)], rd = st.rays[2 * size_t(slot) + 1];
-        const float4 h4 = st.hit[slot];
+        const float4 ro = make_float4(__uint_as_float(in[1 * kShadeThreads]), __uint_as_float(in[2 * kShadeThreads]),
+                                      __uint_as_float(in[3 * kShadeThreads]), __uint_as_float(in[4 * kShadeThreads]));
+        const float4 rd = make_float4(__uint_as_float(in[5 * kShadeThreads]), __uint_as_float(in[6 * kShadeThreads]),
+                                      __uint_as_float(in[7 * kShadeThreads]), __uint_as_float(in[8 * kShadeThreads]));
         pixel = __float_as_uint(ro.w);
         uint32_t bounce = __float_as_uint(rd.w);
         V3 origin = mk(ro.x, ro.y, ro.z), dir = mk(rd.x, rd.y, rd.z);
-        const float4 t4 = st.thr[slot];
-        V3 throughput = mk(t4.x, t4.y, t4.z);
+        V3 throughput = mk(__uint_as_float(in[14 * kShadeThreads]), __uint_as_float(in[15 * kShadeThreads]),
+                           __uint_as_float(in[16 * kShadeThreads]));
         Hit hit;
-        hit.t = h4.x;
-        hit.u = h4.y;
-        hit.v = h4.z;
-        hit.inst = __float_as_uint(h4.w);
+        hit.t = __uint_as_float(in[9 * kShadeThreads]);
+        hit.u = __uint_as_float(in[10 * kShadeThreads]);
+        hit.v = __uint_as_float(in[11 * kShadeThreads]);
+        hit.inst = in[12 * kShadeThreads];
         if (hit.inst == SPK_INVALID_ID)
         {
             if (sc.sky.has_sky)
@@ -308,7 +366,7 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
         }
         else
         {
-            hit.face = st.face[slot];
+            hit.face = in[13 * kShadeThreads];
             Surface sf;
             get_intersection(sc, origin, dir, hit, sf);
             V3 emissive = material_emissive(sc, sc.materials[sf.material], sf.u, sf.v);
@@ -319,8 +377,7 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
             }
             else
             {
-                const uint4 r4 = st.rng[slot];
-                Rng rng{r4.x, r4.y, r4.z, r4.w};
+                Rng rng{in[17 * kShadeThreads], in[18 * kShadeThreads], in[19 * kShadeThreads], in[20 * kShadeThreads]};
                 V3 next_dir;
                 V3 this_throughput = sample_surface(sc, rng, sf, dir, next_dir);
                 throughput = cmul(throughput, this_throughput);
@@ -352,11 +409,12 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
                     if (!done)
                     {
                         origin = sf.location + next_dir * kTolerance;
-                        st.rays[2 * size_t(slot)] = make_float4(origin.x, origin.y, origin.z, ro.w);
-                        st.rays[2 * size_t(slot) + 1] =
-                            make_float4(next_dir.x, next_dir.y, next_dir.z, __uint_as_float(bounce));
-                        st.rng[slot] = make_uint4(rng.s0, rng.s1, rng.s2, rng.s3);
-                        st.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, 0.f);
+                        float4 *r = st.rec + kRec * size_t(slot);
+                        r[0] = make_float4(origin.x, origin.y, origin.z, ro.w);
+                        r[1] = make_float4(next_dir.x, next_dir.y, next_dir.z, __uint_as_float(bounce));
+                        r[4] = make_float4(__uint_as_float(rng.s0), __uint_as_float(rng.s1), __uint_as_float(rng.s2),
+                                           __uint_as_float(rng.s3));
+                        r[5] = make_float4(throughput.x, throughput.y, throughput.z, 0.f);
                         if (a.key_bits)
                         {
                             sort_key = ray_sort_key(a, origin, next_dir);
@@ -418,8 +476,7 @@ static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st, WfSort &sort
 {
     // one allocation, carved into 256-byte aligned arrays
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
-    const size_t b_rays = al(size_t(slots) * 32), b_hit = al(size_t(slots) * 16), b_u32 = al(size_t(slots) * 4),
-                 b_rng = al(size_t(slots) * 16), b_thr = al(size_t(slots) * 16);
+    const size_t b_rec = al(size_t(slots) * kRec * 16), b_u32 = al(size_t(slots) * 4);
     size_t b_sort = 0;
     sort.end_bit = int(3 * key_bits + 3);
     if (key_bits)
@@ -429,7 +486,7 @@ static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st, WfSort &sort
                                                      ctx->stream));
         b_sort = 3 * b_u32 + al(sort.tmp_bytes);
     }
-    const size_t total = b_rays + b_hit + b_u32 * 4 + b_rng + b_thr + 256 + b_sort;
+    const size_t total = b_rec + b_u32 * 3 + 256 + b_sort;
     if (ctx->wf_slots != slots || ctx->wf_bytes < total)
     {
         cudaFree(ctx->wf_block);
@@ -441,16 +498,8 @@ static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st, WfSort &sort
         ctx->wf_bytes = total;
     }
     char *p = static_cast<char *>(ctx->wf_block);
-    st.rays = reinterpret_cast<float4 *>(p);
-    p += b_rays;
-    st.hit = reinterpret_cast<float4 *>(p);
-    p += b_hit;
-    st.rng = reinterpret_cast<uint4 *>(p);
-    p += b_rng;
-    st.thr = reinterpret_cast<float4 *>(p);
-    p += b_thr;
-    st.face = reinterpret_cast<uint32_t *>(p);
-    p += b_u32;
+    st.rec = reinterpret_cast<float4 *>(p);
+    p += b_rec;
     st.queue[0] = reinterpret_cast<uint32_t *>(p);
     p += b_u32;
     st.queue[1] = reinterpret_cast<uint32_t *>(p);
@@ -496,6 +545,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
     unsigned extend_blocks = (slots + kExtendWarps * 32 - 1) / (kExtendWarps * 32);
     const unsigned resident = unsigned(blocks_per_sm) * unsigned(sms); // one wave of persistent CTAs
     extend_blocks = extend_blocks < resident ? extend_blocks : resident;
+    const unsigned regen_blocks = slot_blocks < unsigned(sms) * 8u ? slot_blocks : unsigned(sms) * 8u;
     cudaStream_t s = ctx->stream;
     wf_init_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(st, total);
     ctx->stats.kernel_launches++;
@@ -517,7 +567,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
             st.queue[cur] = q_cur;
             st.queue[cur ^ 1u] = q_nxt;
             wf_shade_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur, ctx->d_accum);
-            wf_regen_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->camera, a, st, cur ^ 1u);
+            wf_regen_kernel<<<regen_blocks, kShadeThreads, 0, s>>>(ctx->camera, a, st, cur ^ 1u);
             wf_advance_kernel<<<1, 1, 0, s>>>(st, cur, ctx->d_counters);
             ctx->stats.kernel_launches += 4;
             if (a.key_bits)
