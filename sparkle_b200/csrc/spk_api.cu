@@ -793,7 +793,7 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     const size_t off_inst = plan.add(size_t(s->num_primitives) * sizeof(DInstance));
     const size_t off_meshes = plan.add(size_t(s->num_meshes) * sizeof(DMesh));
     const size_t off_mats = plan.add(size_t(s->num_materials) * sizeof(DMaterial));
-    const size_t off_tex = plan.add(size_t(s->num_textures) * sizeof(DTexture));
+    const size_t off_tex = plan.add((size_t(s->num_textures) + 6) * sizeof(DTexture)); // + the six faces of a sky map
     struct MeshOffsets
     {
         size_t normals, tangents, indices, uvs, vertices;
@@ -920,8 +920,9 @@ int spk_cuda_upload_scene(SpkContext *ctx, const SpkSceneDesc *s)
     for (int f = 0; sky_map && f < 6; f++)
     {
         add_copy(s->sky.faces[f].pixels, sky_off[f], texture_bytes(s->sky.faces[f]));
-        sky.faces[f] = device_texture(s->sky.faces[f], sky_off[f]);
+        dtex[s->num_textures + f] = device_texture(s->sky.faces[f], sky_off[f]);
     }
+    sky.face_base = s->num_textures;
     static_assert(sizeof(SpkMaterialDesc) == sizeof(DMaterial), "material ABI == device record");
     if (s->num_materials)
     {

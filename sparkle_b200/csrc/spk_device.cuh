@@ -80,7 +80,10 @@ struct DSky
 {
     uint32_t has_sky, has_map;
     float color[3];
-    DTexture faces[6];
+    // the six faces of a sky map are entries face_base .. face_base + 5 of the texture table: a face picked by a run-time
+    // index out of the kernel PARAMETERS made every thread of every kernel that takes a DScene copy the whole struct to
+    // local memory first (wf_shade: 370 B of STL per thread, 4 GB of DRAM write-backs per launch of 16 Mi slots)
+    uint32_t face_base;
 };
 
 struct DCamera

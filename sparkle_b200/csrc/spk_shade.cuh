@@ -556,7 +556,7 @@ __device__ __forceinline__ V3 sky_evaluate(const DScene &sc, V3 d)
         }
         u = (u + 1.f) * 0.5f;
         v = (v + 1.f) * 0.5f;
-        return sample_texture(sc.sky.faces[face], u, v);
+        return sample_texture(sc.textures[sc.sky.face_base + face], u, v);
     }
     float t = 0.5f * d.z + 0.5f;
     return mk(1.f + (sc.sky.color[0] - 1.f) * t, 1.f + (sc.sky.color[1] - 1.f) * t, 1.f + (sc.sky.color[2] - 1.f) * t);

@@ -66,7 +66,11 @@ constexpr int kPersistWarps = 4;
 #endif
 
 template <bool CULL, bool COUNT, int VOTE, bool TOP = false>
+#if SPK_STAGE_RAYS
+__global__ void __launch_bounds__(kPersistWarps * 32, 8) // the staged loop needs the cap to stay at 64 registers
+#else
 __global__ void __launch_bounds__(kPersistWarps * 32)
+#endif
     trace_persistent_kernel(const DScene sc, const float4 *__restrict__ rays, unsigned long long n,
                             float *__restrict__ hits, unsigned long long *__restrict__ counters,
                             unsigned long long *__restrict__ next_ray, uint32_t top_pairs)
@@ -100,7 +104,26 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
             d = mk(rd.x, rd.y, rd.z);
             return true;
         };
-#if SPK_POSTPONE_LEAF
+#if SPK_STAGE_RAYS
+    if (sc.num_instances == 0) // empty scene: every ray misses
+    {
+        const Hit miss{SPK_FLT_MAX, 0.f, 0.f, SPK_INVALID_ID, SPK_INVALID_ID};
+        for (unsigned long long id = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; id < n;
+             id += gridDim.x * (unsigned long long)blockDim.x)
+        {
+            write_hit(id, miss);
+        }
+        return;
+    }
+    if (!TOP)
+    {
+        __shared__ float4 s_stage[kPersistWarps * kStageFloat4PerWarp];
+        warp_trace_loop_staged<CULL, COUNT, SPK_TRACE_REFILL, VOTE, unsigned long long>(
+            sc, n, next_ray, s_lane_words, s_stage, rays, cnt,
+            [](unsigned long long id, uint32_t, uint32_t) { return id; }, write_hit);
+    }
+    else
+#elif SPK_POSTPONE_LEAF
     if (!TOP)
     {
         warp_trace_loop_postponed<CULL, COUNT, SPK_TRACE_REFILL, VOTE>(sc, n, next_ray, s_lane_words, cnt, fetch, write_hit);
@@ -141,7 +164,8 @@ static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, fl
         {
             SPK_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dynamic));
         }
-        const size_t per_cta = sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32 + dynamic;
+        const size_t per_cta = sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32 + dynamic +
+                               (SPK_STAGE_RAYS ? sizeof(float4) * kPersistWarps * kStageFloat4PerWarp : 0);
         // ask for the carve-out that holds 8 CTAs (the register limit) if the array allows it, then see what fits
         SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, per_cta, 8, ctx->opt_carveout));
         SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, dynamic));

@@ -25,6 +25,9 @@
 #ifndef SPK_POSTPONE_LEAF
 #define SPK_POSTPONE_LEAF 0
 #endif
+#ifndef SPK_STAGE_RAYS
+#define SPK_STAGE_RAYS 0 // measured: 8-17 % slower than the plain refill
+#endif
 
 namespace spk
 {
@@ -274,6 +277,138 @@ __device__ __forceinline__ bool lane_tlas_step(const DScene &sc, LaneState &s, L
     stack.push(s.sp, kSentinel);
     s.top = __ldg(&in->root);
     return true;
+}
+
+// ---- ray staging: the refill of warp_trace_loop without its chain of dependent loads ----------------------------------
+// A refill of warp_trace_loop is atomicAdd on the cursor -> (queue entry ->) ray, two or three dependent trips to L2 / HBM
+// during which the whole warp waits, every REFILL rays. Here rays are 32-byte records in ID ORDER ({o.xyz, w0}, {d.xyz, w1}:
+// SpkRay, and the wavefront's ray queue), a warp claims BATCH consecutive ids at a time and copies their rays into its own
+// shared-memory ring with cp.async while the lanes keep traversing: two halves, one being consumed, one in flight. Idle
+// lanes then start from shared memory; only the claim of a new batch (one atomic per BATCH rays) is waited for.
+constexpr int kStageBatch = 16;                       // rays per half
+constexpr int kStageFloat4PerWarp = 2 * kStageBatch * 2 + 1; // two halves x BATCH rays x 2 float4, + the halves' first ids
+static_assert(2 * kStageBatch <= 32, "one cp.async per lane stages a batch");
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+{
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all_but_newest() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// cookie_of(id, w0 bits, w1 bits) -> what store() needs to find the ray's output again (the id, or a slot carried in w0)
+template <bool CULL, bool COUNT, int REFILL, int VOTE, typename Cookie, typename CookieOf, typename Store>
+__device__ __forceinline__ void warp_trace_loop_staged(const DScene &sc, unsigned long long n, unsigned long long *cursor,
+                                                       uint32_t *s_lane_words, float4 *s_stage, const float4 *rays,
+                                                       TraceCounters &cnt, CookieOf &&cookie_of, Store &&store)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    LaneStack stack;
+    stack.sm = s_lane_words + (threadIdx.x >> 5) * (kLaneSmemWords * 32) + lane;
+    float4 *ring = s_stage + (threadIdx.x >> 5) * kStageFloat4PerWarp;
+    LaneState s;
+    s.top = 0u;
+    s.inst = SPK_INVALID_ID;
+    Cookie cookie = Cookie();
+    bool active = false, started = false;
+    bool exhausted = false;             // warp-uniform: the cursor has passed n, batches claimed from now on are empty
+    unsigned long long *half_base = reinterpret_cast<unsigned long long *>(ring + 2 * kStageBatch * 2); // [2] first ray ids
+    int half_cnts = 0;                  // rays staged in half 0 | half 1 << 8
+    int cur = 0, off = 0;               // half being consumed, rays of it already handed out
+    const float4 *__restrict__ pairs = sc.pairs;
+    auto claim = [&](int half) {
+        unsigned long long b = 0;
+        int c = 0;
+        if (!exhausted)
+        {
+            if (lane == 0)
+            {
+                b = atomicAdd(cursor, (unsigned long long)kStageBatch);
+            }
+            b = __shfl_sync(0xffffffffu, b, 0);
+            c = b >= n ? 0 : (n - b < (unsigned long long)kStageBatch ? int(n - b) : kStageBatch);
+            exhausted = b + kStageBatch >= n;
+            if ((int)lane < 2 * c) // two lanes per ray, 16 bytes each: the batch is one contiguous run
+            {
+                cp_async16(ring + half * (2 * kStageBatch) + lane, rays + 2 * b + lane);
+            }
+        }
+        cp_async_commit(); // an empty group once exhausted: "all but the newest" stays the half being consumed
+        if (lane == 0)
+        {
+            half_base[half] = b;
+        }
+        half_cnts = half ? ((half_cnts & 0xff) | (c << 8)) : ((half_cnts & 0xff00) | c);
+    };
+    claim(0);
+    claim(1);
+    for (;;)
+    {
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        const int cur_cnt = (half_cnts >> (8 * cur)) & 0xff;
+        const int have = cur_cnt - off;
+        if (have == 0 && idle == 0xffffffffu)
+        {
+            break; // a drained half is re-claimed at once: an empty one means the cursor is past n and nothing is in flight
+        }
+        if (have > 0 && (__popc(idle) >= REFILL || idle == 0xffffffffu))
+        {
+            cp_async_wait_all_but_newest();
+            __syncwarp();
+            const int take = __popc(idle) < have ? __popc(idle) : have;
+            const int r = __popc(idle & lt_mask);
+            if (!active && r < take)
+            {
+                const int e = off + r;
+                const float4 a = ring[cur * (2 * kStageBatch) + 2 * e], b = ring[cur * (2 * kStageBatch) + 2 * e + 1];
+                cookie = cookie_of(half_base[cur] + e, __float_as_uint(a.w), __float_as_uint(b.w));
+                lane_begin<CULL>(sc, s, stack, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z));
+                active = true;
+                started = true;
+            }
+            off += take;
+            if (off == cur_cnt)
+            {
+                __syncwarp(); // every lane has read its ray before the half is overwritten
+                claim(cur);
+                cur ^= 1;
+                off = 0;
+            }
+        }
+        const bool is_inner = active && (s.top & 15u) == 0u;
+        const bool is_tri = active && !is_inner && s.inst != SPK_INVALID_ID;
+        const bool is_tlas = active && !is_inner && s.inst == SPK_INVALID_ID;
+        const int c_inner = __popc(__ballot_sync(0xffffffffu, is_inner));
+        const int c_tri = __popc(__ballot_sync(0xffffffffu, is_tri));
+        const int c_tlas = __popc(__ballot_sync(0xffffffffu, is_tlas));
+        const bool run_tri = c_tri >= VOTE || (c_inner == 0 && c_tri > 0 && c_tri >= c_tlas);
+        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (c_inner == 0 && c_tlas > 0));
+        if (run_tri)
+        {
+            if (is_tri)
+            {
+                active = lane_tri_step<COUNT>(sc, s, stack, cnt);
+            }
+        }
+        else if (run_tlas)
+        {
+            if (is_tlas)
+            {
+                active = lane_tlas_step<COUNT>(sc, s, stack, cnt);
+            }
+        }
+        else if (is_inner)
+        {
+            active = lane_inner_step<CULL, COUNT, false>(pairs, s, stack, cnt);
+        }
+        if (!active && started)
+        {
+            store(cookie, s.best);
+            started = false;
+        }
+    }
 }
 
 // ---- postponed-leaf form of the lane state machine (SPK_POSTPONE_LEAF) ----------------------------------------------
