@@ -66,11 +66,7 @@ constexpr int kPersistWarps = 4;
 #endif
 
 template <bool CULL, bool COUNT, int VOTE, bool TOP = false>
-#if SPK_STAGE_RAYS
-__global__ void __launch_bounds__(kPersistWarps * 32, 8) // the staged loop needs the cap to stay at 64 registers
-#else
 __global__ void __launch_bounds__(kPersistWarps * 32)
-#endif
     trace_persistent_kernel(const DScene sc, const float4 *__restrict__ rays, unsigned long long n,
                             float *__restrict__ hits, unsigned long long *__restrict__ counters,
                             unsigned long long *__restrict__ next_ray, uint32_t top_pairs)
@@ -92,7 +88,9 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
         o[3] = __uint_as_float(prim);
         o[4] = __uint_as_float(best.face);
     };
-    auto fetch = [&](unsigned long long id, V3 &o, V3 &d) {
+    warp_trace_loop<CULL, COUNT, SPK_TRACE_REFILL, VOTE, TOP>(
+        sc, n, next_ray, s_lane_words, cnt, ~0ull,
+        [&](unsigned long long id, V3 &o, V3 &d, unsigned long long &cookie) {
             if (sc.num_instances == 0)
             {
                 Hit miss{SPK_FLT_MAX, 0.f, 0.f, SPK_INVALID_ID, SPK_INVALID_ID}; // empty scene: every ray misses
@@ -102,37 +100,10 @@ __global__ void __launch_bounds__(kPersistWarps * 32)
             float4 ro = __ldg(rays + 2 * id), rd = __ldg(rays + 2 * id + 1);
             o = mk(ro.x, ro.y, ro.z);
             d = mk(rd.x, rd.y, rd.z);
+            cookie = id;
             return true;
-        };
-#if SPK_STAGE_RAYS
-    if (sc.num_instances == 0) // empty scene: every ray misses
-    {
-        const Hit miss{SPK_FLT_MAX, 0.f, 0.f, SPK_INVALID_ID, SPK_INVALID_ID};
-        for (unsigned long long id = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; id < n;
-             id += gridDim.x * (unsigned long long)blockDim.x)
-        {
-            write_hit(id, miss);
-        }
-        return;
-    }
-    if (!TOP)
-    {
-        __shared__ float4 s_stage[kPersistWarps * kStageFloat4PerWarp];
-        warp_trace_loop_staged<CULL, COUNT, SPK_TRACE_REFILL, VOTE, unsigned long long>(
-            sc, n, next_ray, s_lane_words, s_stage, rays, cnt,
-            [](unsigned long long id, uint32_t, uint32_t) { return id; }, write_hit);
-    }
-    else
-#elif SPK_POSTPONE_LEAF
-    if (!TOP)
-    {
-        warp_trace_loop_postponed<CULL, COUNT, SPK_TRACE_REFILL, VOTE>(sc, n, next_ray, s_lane_words, cnt, fetch, write_hit);
-    }
-    else
-#endif
-    {
-        warp_trace_loop<CULL, COUNT, SPK_TRACE_REFILL, VOTE, TOP>(sc, n, next_ray, s_lane_words, cnt, fetch, write_hit, top);
-    }
+        },
+        write_hit, top);
     if (COUNT)
     {
         const unsigned lane = threadIdx.x & 31u;
@@ -164,8 +135,7 @@ static int launch_persistent(SpkContext *ctx, const float4 *rays, uint64_t n, fl
         {
             SPK_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dynamic));
         }
-        const size_t per_cta = sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32 + dynamic +
-                               (SPK_STAGE_RAYS ? sizeof(float4) * kPersistWarps * kStageFloat4PerWarp : 0);
+        const size_t per_cta = sizeof(uint32_t) * kPersistWarps * kLaneSmemWords * 32 + dynamic;
         // ask for the carve-out that holds 8 CTAs (the register limit) if the array allows it, then see what fits
         SPK_CUDA_TRY(spk::prefer_small_carveout(kernel, per_cta, 8, ctx->opt_carveout));
         SPK_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kPersistWarps * 32, dynamic));

@@ -22,13 +22,6 @@
 #pragma once
 #include "spk_traverse.cuh"
 
-#ifndef SPK_POSTPONE_LEAF
-#define SPK_POSTPONE_LEAF 0
-#endif
-#ifndef SPK_STAGE_RAYS
-#define SPK_STAGE_RAYS 0 // measured: 8-17 % slower than the plain refill
-#endif
-
 namespace spk
 {
 constexpr uint32_t kSentinel = 0xFFFFFFFFu; // stack marker: "leave the instance, back to the TLAS"
@@ -279,414 +272,16 @@ __device__ __forceinline__ bool lane_tlas_step(const DScene &sc, LaneState &s, L
     return true;
 }
 
-// ---- ray staging: the refill of warp_trace_loop without its chain of dependent loads ----------------------------------
-// A refill of warp_trace_loop is atomicAdd on the cursor -> (queue entry ->) ray, two or three dependent trips to L2 / HBM
-// during which the whole warp waits, every REFILL rays. Here rays are 32-byte records in ID ORDER ({o.xyz, w0}, {d.xyz, w1}:
-// SpkRay, and the wavefront's ray queue), a warp claims BATCH consecutive ids at a time and copies their rays into its own
-// shared-memory ring with cp.async while the lanes keep traversing: two halves, one being consumed, one in flight. Idle
-// lanes then start from shared memory; only the claim of a new batch (one atomic per BATCH rays) is waited for.
-constexpr int kStageBatch = 16;                       // rays per half
-constexpr int kStageFloat4PerWarp = 2 * kStageBatch * 2 + 1; // two halves x BATCH rays x 2 float4, + the halves' first ids
-static_assert(2 * kStageBatch <= 32, "one cp.async per lane stages a batch");
-
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
-{
-    const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all_but_newest() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
-
-// cookie_of(id, w0 bits, w1 bits) -> what store() needs to find the ray's output again (the id, or a slot carried in w0)
-template <bool CULL, bool COUNT, int REFILL, int VOTE, typename Cookie, typename CookieOf, typename Store>
-__device__ __forceinline__ void warp_trace_loop_staged(const DScene &sc, unsigned long long n, unsigned long long *cursor,
-                                                       uint32_t *s_lane_words, float4 *s_stage, const float4 *rays,
-                                                       TraceCounters &cnt, CookieOf &&cookie_of, Store &&store)
-{
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    LaneStack stack;
-    stack.sm = s_lane_words + (threadIdx.x >> 5) * (kLaneSmemWords * 32) + lane;
-    float4 *ring = s_stage + (threadIdx.x >> 5) * kStageFloat4PerWarp;
-    LaneState s;
-    s.top = 0u;
-    s.inst = SPK_INVALID_ID;
-    Cookie cookie = Cookie();
-    bool active = false, started = false;
-    bool exhausted = false;             // warp-uniform: the cursor has passed n, batches claimed from now on are empty
-    unsigned long long *half_base = reinterpret_cast<unsigned long long *>(ring + 2 * kStageBatch * 2); // [2] first ray ids
-    int half_cnts = 0;                  // rays staged in half 0 | half 1 << 8
-    int cur = 0, off = 0;               // half being consumed, rays of it already handed out
-    const float4 *__restrict__ pairs = sc.pairs;
-    auto claim = [&](int half) {
-        unsigned long long b = 0;
-        int c = 0;
-        if (!exhausted)
-        {
-            if (lane == 0)
-            {
-                b = atomicAdd(cursor, (unsigned long long)kStageBatch);
-            }
-            b = __shfl_sync(0xffffffffu, b, 0);
-            c = b >= n ? 0 : (n - b < (unsigned long long)kStageBatch ? int(n - b) : kStageBatch);
-            exhausted = b + kStageBatch >= n;
-            if ((int)lane < 2 * c) // two lanes per ray, 16 bytes each: the batch is one contiguous run
-            {
-                cp_async16(ring + half * (2 * kStageBatch) + lane, rays + 2 * b + lane);
-            }
-        }
-        cp_async_commit(); // an empty group once exhausted: "all but the newest" stays the half being consumed
-        if (lane == 0)
-        {
-            half_base[half] = b;
-        }
-        half_cnts = half ? ((half_cnts & 0xff) | (c << 8)) : ((half_cnts & 0xff00) | c);
-    };
-    claim(0);
-    claim(1);
-    for (;;)
-    {
-        const unsigned idle = __ballot_sync(0xffffffffu, !active);
-        const int cur_cnt = (half_cnts >> (8 * cur)) & 0xff;
-        const int have = cur_cnt - off;
-        if (have == 0 && idle == 0xffffffffu)
-        {
-            break; // a drained half is re-claimed at once: an empty one means the cursor is past n and nothing is in flight
-        }
-        if (have > 0 && (__popc(idle) >= REFILL || idle == 0xffffffffu))
-        {
-            cp_async_wait_all_but_newest();
-            __syncwarp();
-            const int take = __popc(idle) < have ? __popc(idle) : have;
-            const int r = __popc(idle & lt_mask);
-            if (!active && r < take)
-            {
-                const int e = off + r;
-                const float4 a = ring[cur * (2 * kStageBatch) + 2 * e], b = ring[cur * (2 * kStageBatch) + 2 * e + 1];
-                cookie = cookie_of(half_base[cur] + e, __float_as_uint(a.w), __float_as_uint(b.w));
-                lane_begin<CULL>(sc, s, stack, mk(a.x, a.y, a.z), mk(b.x, b.y, b.z));
-                active = true;
-                started = true;
-            }
-            off += take;
-            if (off == cur_cnt)
-            {
-                __syncwarp(); // every lane has read its ray before the half is overwritten
-                claim(cur);
-                cur ^= 1;
-                off = 0;
-            }
-        }
-        const bool is_inner = active && (s.top & 15u) == 0u;
-        const bool is_tri = active && !is_inner && s.inst != SPK_INVALID_ID;
-        const bool is_tlas = active && !is_inner && s.inst == SPK_INVALID_ID;
-        const int c_inner = __popc(__ballot_sync(0xffffffffu, is_inner));
-        const int c_tri = __popc(__ballot_sync(0xffffffffu, is_tri));
-        const int c_tlas = __popc(__ballot_sync(0xffffffffu, is_tlas));
-        const bool run_tri = c_tri >= VOTE || (c_inner == 0 && c_tri > 0 && c_tri >= c_tlas);
-        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (c_inner == 0 && c_tlas > 0));
-        if (run_tri)
-        {
-            if (is_tri)
-            {
-                active = lane_tri_step<COUNT>(sc, s, stack, cnt);
-            }
-        }
-        else if (run_tlas)
-        {
-            if (is_tlas)
-            {
-                active = lane_tlas_step<COUNT>(sc, s, stack, cnt);
-            }
-        }
-        else if (is_inner)
-        {
-            active = lane_inner_step<CULL, COUNT, false>(pairs, s, stack, cnt);
-        }
-        if (!active && started)
-        {
-            store(cookie, s.best);
-            started = false;
-        }
-    }
-}
-
-// ---- postponed-leaf form of the lane state machine (SPK_POSTPONE_LEAF) ----------------------------------------------
-// A lane that reaches a triangle leaf does not wait for the warp's next triangle step: it parks the leaf in `pend` and goes
-// on with the inner nodes on its stack (speculative traversal, Aila & Laine 2009); only a second leaf, the end of the
-// instance (the sentinel) or an empty stack make it wait. A triangle step then serves EVERY lane that has a parked leaf,
-// waiting or not. Leaves are still tested in the order the traversal reaches them (pend before top), and a bound that is
-// shortened later only ever skips nodes that cannot hold a closer hit, so the closest hit is the same, bit for bit; the
-// culled form visits a few more nodes than the in-order loop because its bound lags by one leaf.
-constexpr uint32_t kEmptyStack = 0xFFFFFFFDu; // `top` of a lane whose stack ran empty (low nibble != 0: not an inner node)
-enum LaneMode : int
-{
-    kLaneIdle = 0,
-    kLaneInner = 1,
-    kLaneWaitTri = 2,
-    kLaneWaitTlas = 3
-};
-
-__device__ __forceinline__ void lane_leave_instance(LaneState &s, LaneStack &stack)
-{
-    s.inst = SPK_INVALID_ID;
-    s.lo = s.wo;
-    s.ld = s.wd;
-    const float *w = reinterpret_cast<const float *>(stack.sm) + kSmemStack * 32;
-    s.sr.ix = w[0];
-    s.sr.iy = w[32];
-    s.sr.iz = w[64];
-    s.sr.ox = w[96];
-    s.sr.oy = w[128];
-    s.sr.oz = w[160];
-    s.sr.nx = signbit(s.wd.x);
-    s.sr.ny = signbit(s.wd.y);
-    s.sr.nz = signbit(s.wd.z);
-}
-
-__device__ __forceinline__ uint32_t lane_next(LaneState &s, LaneStack &stack)
-{
-    return s.sp ? stack.pop(s.sp) : kEmptyStack;
-}
-
-// bring a lane to the next thing it can do: park a triangle leaf, leave an instance, ... until `top` is an inner node or the
-// lane has to wait
-__device__ __forceinline__ int lane_settle(LaneState &s, LaneStack &stack, uint32_t &pend)
-{
-    for (;;)
-    {
-        const uint32_t top = s.top;
-        if ((top & 15u) == 0u)
-        {
-            return kLaneInner;
-        }
-        if (top == kEmptyStack)
-        {
-            return pend ? kLaneWaitTri : kLaneIdle;
-        }
-        if (top == kSentinel)
-        {
-            if (pend)
-            {
-                return kLaneWaitTri; // the parked leaf belongs to this instance: test it before the ray goes back
-            }
-            lane_leave_instance(s, stack);
-        }
-        else if (s.inst != SPK_INVALID_ID)
-        {
-            if (pend)
-            {
-                return kLaneWaitTri;
-            }
-            pend = top;
-        }
-        else
-        {
-            return kLaneWaitTlas;
-        }
-        s.top = lane_next(s, stack);
-    }
-}
-
-template <bool CULL, bool COUNT>
-__device__ __forceinline__ void lane_inner_step_np(const float4 *__restrict__ pairs, LaneState &s, LaneStack &stack,
-                                                   TraceCounters &cnt)
-{
-    const float4 *p = pairs + size_t(s.top >> 4) * 4;
-    float4 l0, l1, r0, r1;
-    ldg256(p, l0, l1);
-    ldg256(p + 2, r0, r1);
-    if (COUNT)
-    {
-        cnt.node_visits++;
-    }
-    bool hl, hr;
-    float tl = slab(s.sr, l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, hl);
-    float tr = slab(s.sr, r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, hr);
-    if (CULL)
-    {
-        float bound = s.best.t + (s.best.t * 2.44140625e-4f + s.slack_abs);
-        hl = hl && tl <= bound;
-        hr = hr && tr <= bound;
-    }
-    const uint32_t li = __float_as_uint(l1.z), ri = __float_as_uint(r1.z);
-    if (hl)
-    {
-        uint32_t near_i = li;
-        if (hr)
-        {
-            uint32_t far_i = ri;
-            if (tl > tr)
-            {
-                near_i = ri;
-                far_i = li;
-            }
-            stack.push(s.sp, far_i);
-        }
-        s.top = near_i;
-    }
-    else
-    {
-        s.top = hr ? ri : lane_next(s, stack);
-    }
-}
-
-// one triangle of the parked leaf
-template <bool COUNT>
-__device__ __forceinline__ void lane_pend_step(const DScene &sc, LaneState &s, uint32_t &pend, TraceCounters &cnt)
-{
-    const uint32_t first = pend >> 4, count = pend & 15u;
-    const float fwd_row0[4] = {s.f0, s.f1, s.f2, s.f3};
-    if (COUNT)
-    {
-        cnt.tri_tests++;
-    }
-    intersect_triangle(sc.tris + size_t(first) * 3, s.lo, s.ld, s.wo, s.wd, fwd_row0, s.inst, s.best);
-    pend = count > 1u ? (((first + 1u) << 4) | (count - 1u)) : 0u;
-}
-
-// TLAS leaf in `top` (lane_tlas_step without the pop)
-template <bool COUNT>
-__device__ __forceinline__ void lane_tlas_step_np(const DScene &sc, LaneState &s, LaneStack &stack, TraceCounters &cnt)
-{
-    const uint32_t first = s.top >> 4, count = s.top & 15u;
-    if (count > 1u)
-    {
-        stack.push(s.sp, ((first + 1u) << 4) | (count - 1u));
-    }
-    const DInstance *__restrict__ in = sc.instances + first;
-    if (__ldg(&in->kind) == 1u)
-    {
-        if (COUNT)
-        {
-            cnt.sphere_tests++;
-        }
-        intersect_sphere(in, s.wo, s.wd, first, s.best);
-        s.top = lane_next(s, stack);
-        return;
-    }
-    if (COUNT)
-    {
-        cnt.inst_visits++;
-    }
-    float inv[12];
-    const float4 *m = reinterpret_cast<const float4 *>(in);
-#pragma unroll
-    for (int k = 0; k < 3; k++)
-    {
-        float4 a = __ldg(m + k);
-        inv[4 * k] = a.x;
-        inv[4 * k + 1] = a.y;
-        inv[4 * k + 2] = a.z;
-        inv[4 * k + 3] = a.w;
-    }
-    float4 f = __ldg(m + 3);
-    s.f0 = f.x;
-    s.f1 = f.y;
-    s.f2 = f.z;
-    s.f3 = f.w;
-    s.lo = xform_point(inv, s.wo);
-    s.ld = xform_dir(inv, s.wd);
-    s.sr = make_slab_ray(s.lo, s.ld);
-    s.inst = first;
-    stack.push(s.sp, kSentinel);
-    s.top = __ldg(&in->root);
-}
-
-template <bool CULL, bool COUNT, int REFILL, int VOTE, typename Fetch, typename Store>
-__device__ __forceinline__ void warp_trace_loop_postponed(const DScene &sc, unsigned long long n, unsigned long long *cursor,
-                                                          uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch,
-                                                          Store &&store)
-{
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    LaneStack stack;
-    stack.sm = s_lane_words + (threadIdx.x >> 5) * (kLaneSmemWords * 32) + lane;
-    LaneState s;
-    s.top = kEmptyStack;
-    s.inst = SPK_INVALID_ID;
-    s.sp = 0;
-    uint32_t pend = 0;
-    int mode = kLaneIdle;
-    unsigned long long ray_id = ~0ull;
-    bool exhausted = false;
-    const float4 *__restrict__ pairs = sc.pairs;
-    for (;;)
-    {
-        const unsigned idle = __ballot_sync(0xffffffffu, mode == kLaneIdle);
-        if (idle == 0xffffffffu && exhausted)
-        {
-            break;
-        }
-        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xffffffffu))
-        {
-            unsigned long long base = 0;
-            const int leader = __ffs(idle) - 1;
-            if ((int)lane == leader)
-            {
-                base = atomicAdd(cursor, (unsigned long long)__popc(idle));
-            }
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (mode == kLaneIdle)
-            {
-                unsigned long long id = base + __popc(idle & lt_mask);
-                V3 o, d;
-                if (id < n && fetch(id, o, d))
-                {
-                    lane_begin<CULL>(sc, s, stack, o, d);
-                    ray_id = id;
-                    pend = 0;
-                    mode = lane_settle(s, stack, pend);
-                }
-            }
-            exhausted = base + __popc(idle) >= n;
-        }
-        const int c_inner = __popc(__ballot_sync(0xffffffffu, mode == kLaneInner));
-        const int c_tri = __popc(__ballot_sync(0xffffffffu, mode == kLaneWaitTri));
-        const int c_tlas = __popc(__ballot_sync(0xffffffffu, mode == kLaneWaitTlas));
-        const bool run_tri = c_tri >= VOTE || (c_inner == 0 && c_tri > 0 && c_tri >= c_tlas);
-        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (c_inner == 0 && c_tlas > 0));
-        if (run_tri)
-        {
-            if (pend) // waiting lanes and lanes that are still walking with a parked leaf
-            {
-                lane_pend_step<COUNT>(sc, s, pend, cnt);
-                if (mode == kLaneWaitTri)
-                {
-                    mode = lane_settle(s, stack, pend);
-                }
-            }
-        }
-        else if (run_tlas)
-        {
-            if (mode == kLaneWaitTlas)
-            {
-                lane_tlas_step_np<COUNT>(sc, s, stack, cnt);
-                mode = lane_settle(s, stack, pend);
-            }
-        }
-        else if (mode == kLaneInner)
-        {
-            lane_inner_step_np<CULL, COUNT>(pairs, s, stack, cnt);
-            mode = lane_settle(s, stack, pend);
-        }
-        if (mode == kLaneIdle && ray_id != ~0ull)
-        {
-            store(ray_id, s.best);
-            ray_id = ~0ull;
-        }
-    }
-}
-
 /*
- * The persistent loop of one warp. `cursor` is the global ray counter, n the number of rays; fetch(id, o, d) loads ray
- * id and returns false to skip it, store(id, best) writes its closest hit. REFILL: idle lanes wait until this many are
+ * The persistent loop of one warp. `cursor` is the global ray counter, n the number of rays; fetch(id, o, d, cookie)
+ * loads ray id, sets the lane's cookie (the id, or whatever names the ray's output) and returns false to skip the ray,
+ * store(cookie, best) writes its closest hit. REFILL: idle lanes wait until this many are
  * idle (or nothing else is left to do) before one lane fetches a block of ray ids with a single atomic.
  */
-template <bool CULL, bool COUNT, int REFILL, int VOTE, bool TOP = false, typename Fetch, typename Store>
+template <bool CULL, bool COUNT, int REFILL, int VOTE, bool TOP = false, typename Cookie, typename Fetch, typename Store>
 __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long long n, unsigned long long *cursor,
-                                                uint32_t *s_lane_words, TraceCounters &cnt, Fetch &&fetch, Store &&store,
-                                                const TopOfTree &top = TopOfTree{nullptr, 0, 0})
+                                                uint32_t *s_lane_words, TraceCounters &cnt, Cookie no_ray, Fetch &&fetch,
+                                                Store &&store, const TopOfTree &top = TopOfTree{nullptr, 0, 0})
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -695,7 +290,7 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
     LaneState s;
     s.top = 0u;
     s.inst = SPK_INVALID_ID;
-    unsigned long long ray_id = ~0ull;
+    Cookie cookie = no_ray; // what store() needs to find the ray's output again; no_ray while the lane has none
     bool active = false;
     bool exhausted = false; // warp-uniform: the global counter has passed n
     const float4 *__restrict__ pairs = sc.pairs;
@@ -720,10 +315,9 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
             {
                 unsigned long long id = base + __popc(idle & lt_mask);
                 V3 o, d;
-                if (id < n && fetch(id, o, d))
+                if (id < n && fetch(id, o, d, cookie))
                 {
                     lane_begin<CULL>(sc, s, stack, o, d);
-                    ray_id = id;
                     active = true;
                 }
             }
@@ -760,10 +354,10 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
             active = lane_inner_step<CULL, COUNT, TOP>(pairs, s, stack, cnt, top);
         }
         // lanes whose stack ran empty: the ray is finished
-        if (!active && ray_id != ~0ull)
+        if (!active && cookie != no_ray)
         {
-            store(ray_id, s.best);
-            ray_id = ~0ull;
+            store(cookie, s.best);
+            cookie = no_ray;
         }
     }
 }

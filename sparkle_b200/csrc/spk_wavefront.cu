@@ -34,6 +34,18 @@ constexpr int kShadeThreads = 256;
 constexpr int kExtendWarps = 4;
 constexpr uint32_t kEmptySlot = 0xFFFFFFFFu;
 constexpr size_t kRec = 6; // float4 per slot record
+// The slot records stream through the memory system once per iteration (1.6 GB for 16 Mi slots): they are read and
+// written with the evict-first hint so that they do not push the BVH and the mesh attributes out of the L2.
+#ifndef SPK_WF_STREAM
+#define SPK_WF_STREAM 1
+#endif
+#if SPK_WF_STREAM
+#define SPK_LD(p) __ldcs(p)
+#define SPK_ST(p, v) __stcs(p, v)
+#else
+#define SPK_LD(p) (*(p))
+#define SPK_ST(p, v) (*(p) = (v))
+#endif
 
 struct WfCtrl
 {
@@ -169,10 +181,10 @@ __global__ void __launch_bounds__(kShadeThreads)
         V3 target = lower_left + u * max_u + v * max_v;
         V3 dir = normalized(target - origin);
         float4 *r = st.rec + kRec * size_t(slot);
-        r[0] = make_float4(origin.x, origin.y, origin.z, __uint_as_float(p));
-        r[1] = make_float4(dir.x, dir.y, dir.z, __uint_as_float(0u));
-        r[4] = make_float4(__uint_as_float(rng.s0), __uint_as_float(rng.s1), __uint_as_float(rng.s2), __uint_as_float(rng.s3));
-        r[5] = make_float4(1.f, 1.f, 1.f, 0.f);
+        SPK_ST(r + 0, make_float4(origin.x, origin.y, origin.z, __uint_as_float(p)));
+        SPK_ST(r + 1, make_float4(dir.x, dir.y, dir.z, __uint_as_float(0u)));
+        SPK_ST(r + 4, make_float4(__uint_as_float(rng.s0), __uint_as_float(rng.s1), __uint_as_float(rng.s2), __uint_as_float(rng.s3)));
+        SPK_ST(r + 5, make_float4(1.f, 1.f, 1.f, 0.f));
         st.queue[nxt][c.n_queue[nxt] + k] = slot; // after the entries wf_shade appended; wf_advance adds the count
         if (a.key_bits)
         {
@@ -212,24 +224,20 @@ __global__ void __launch_bounds__(kExtendWarps * 32, SPK_WF_EXTEND_CTAS)
 #ifndef SPK_WF_VOTE
 #define SPK_WF_VOTE 8
 #endif
-#if SPK_POSTPONE_LEAF
-    warp_trace_loop_postponed<CULL, COUNT, REFILL, SPK_WF_VOTE>(
-#else
     warp_trace_loop<CULL, COUNT, REFILL, SPK_WF_VOTE>(
-#endif
-        sc, st.ctrl->n_queue[q], &st.ctrl->next_ray, s_lane_words, cnt,
-        [&](unsigned long long id, V3 &o, V3 &d) {
+        sc, st.ctrl->n_queue[q], &st.ctrl->next_ray, s_lane_words, cnt, kEmptySlot,
+        [&](unsigned long long id, V3 &o, V3 &d, uint32_t &slot_out) {
             const uint32_t slot = __ldg(queue + id);
-            float4 ro = rec[kRec * size_t(slot)], rd = rec[kRec * size_t(slot) + 1];
+            float4 ro = SPK_LD(rec + kRec * size_t(slot)), rd = SPK_LD(rec + kRec * size_t(slot) + 1);
             o = mk(ro.x, ro.y, ro.z);
             d = mk(rd.x, rd.y, rd.z);
+            slot_out = slot; // kept by the lane: the store used to read the queue again, a dependent load per finished ray
             return true;
         },
-        [&](unsigned long long id, const Hit &best) {
-            const uint32_t slot = __ldg(queue + id);
+        [&](uint32_t slot, const Hit &best) {
             float4 *r = st.rec + kRec * size_t(slot) + 2;
-            r[0] = make_float4(best.t, best.u, best.v, __uint_as_float(best.inst));
-            r[1] = make_float4(__uint_as_float(best.face), 0.f, 0.f, 0.f); // the whole sector: no fill for a partial write
+            SPK_ST(r + 0, make_float4(best.t, best.u, best.v, __uint_as_float(best.inst)));
+            SPK_ST(r + 1, make_float4(__uint_as_float(best.face), 0.f, 0.f, 0.f)); // the whole sector: no fill for a partial write
         });
     if (COUNT)
     {
@@ -281,13 +289,13 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
     {
         my = st.queue[cur][k];
         const float4 *r = st.rec + kRec * size_t(my);
-        q_ro = r[0];
-        q_rd = r[1];
-        q_h = r[2];
-        q_face = __float_as_uint(r[3].x);
-        const float4 g = r[4];
+        q_ro = SPK_LD(r + 0);
+        q_rd = SPK_LD(r + 1);
+        q_h = SPK_LD(r + 2);
+        q_face = __float_as_uint(SPK_LD(r + 3).x);
+        const float4 g = SPK_LD(r + 4);
         q_rng = make_uint4(__float_as_uint(g.x), __float_as_uint(g.y), __float_as_uint(g.z), __float_as_uint(g.w));
-        q_t = r[5];
+        q_t = SPK_LD(r + 5);
         key = shade_class(sc, __float_as_uint(q_h.w));
     }
     pos = atomicAdd(&s_bin[key], 1u);
@@ -410,11 +418,11 @@ __global__ void __launch_bounds__(kShadeThreads, SPK_WF_SHADE_CTAS)
                     {
                         origin = sf.location + next_dir * kTolerance;
                         float4 *r = st.rec + kRec * size_t(slot);
-                        r[0] = make_float4(origin.x, origin.y, origin.z, ro.w);
-                        r[1] = make_float4(next_dir.x, next_dir.y, next_dir.z, __uint_as_float(bounce));
-                        r[4] = make_float4(__uint_as_float(rng.s0), __uint_as_float(rng.s1), __uint_as_float(rng.s2),
-                                           __uint_as_float(rng.s3));
-                        r[5] = make_float4(throughput.x, throughput.y, throughput.z, 0.f);
+                        SPK_ST(r + 0, make_float4(origin.x, origin.y, origin.z, ro.w));
+                        SPK_ST(r + 1, make_float4(next_dir.x, next_dir.y, next_dir.z, __uint_as_float(bounce)));
+                        SPK_ST(r + 4, make_float4(__uint_as_float(rng.s0), __uint_as_float(rng.s1), __uint_as_float(rng.s2),
+                                                  __uint_as_float(rng.s3)));
+                        SPK_ST(r + 5, make_float4(throughput.x, throughput.y, throughput.z, 0.f));
                         if (a.key_bits)
                         {
                             sort_key = ray_sort_key(a, origin, next_dir);
