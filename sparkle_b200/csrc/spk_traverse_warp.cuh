@@ -26,7 +26,10 @@ namespace spk
 {
 constexpr uint32_t kSentinel = 0xFFFFFFFFu; // stack marker: "leave the instance, back to the TLAS"
 constexpr int kWarpStack = 68;              // 32 TLAS + 1 leaf remainder + 1 sentinel + 32 BLAS (+2 spare)
-constexpr int kSmemStack = 24;              // entries per lane kept in shared memory; deeper ones spill to local memory
+#ifndef SPK_SMEM_STACK
+#define SPK_SMEM_STACK 24
+#endif
+constexpr int kSmemStack = SPK_SMEM_STACK;              // entries per lane kept in shared memory; deeper ones spill to local memory
 constexpr int kLaneSmemWords = kSmemStack + 6; // + the world-space slab constants
 
 // Per-lane traversal stack. The first kSmemStack entries live in shared memory as [depth][lane]: bank = lane whatever
@@ -297,7 +300,7 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
     for (;;)
     {
         // ---- refill idle lanes from the global ray counter
-        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        unsigned idle = __ballot_sync(0xffffffffu, !active);
         if (idle == 0xffffffffu && exhausted)
         {
             break;
@@ -322,19 +325,20 @@ __device__ __forceinline__ void warp_trace_loop(const DScene &sc, unsigned long 
                 }
             }
             exhausted = base + __popc(idle) >= n;
+            idle = __ballot_sync(0xffffffffu, !active);
         }
         // ---- majority vote: the state most lanes are in runs one step
         const bool is_inner = active && (s.top & 15u) == 0u;
         const bool is_tri = active && !is_inner && s.inst != SPK_INVALID_ID;
         const bool is_tlas = active && !is_inner && s.inst == SPK_INVALID_ID;
-        const int c_inner = __popc(__ballot_sync(0xffffffffu, is_inner));
-        const int c_tri = __popc(__ballot_sync(0xffffffffu, is_tri));
-        const int c_tlas = __popc(__ballot_sync(0xffffffffu, is_tlas));
+        const unsigned m_tri = __ballot_sync(0xffffffffu, is_tri), m_tlas = __ballot_sync(0xffffffffu, is_tlas);
+        const bool no_inner = (~idle & ~(m_tri | m_tlas)) == 0u; // every active lane waits in a leaf state
+        const int c_tri = __popc(m_tri), c_tlas = __popc(m_tlas);
         // a leaf state runs as soon as VOTE lanes wait in it (or nothing else can run); inner steps otherwise. A pure
         // majority vote starves the rare state: on soup-1M 6 % of the steps are triangles, their lanes waited until they
         // outnumbered the inner lanes, and inner steps ran with 13.7 lanes (profiles/r1_trace_majority_vote_ncu.txt)
-        const bool run_tri = c_tri >= VOTE || (c_inner == 0 && c_tri > 0 && c_tri >= c_tlas);
-        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (c_inner == 0 && c_tlas > 0));
+        const bool run_tri = c_tri >= VOTE || (no_inner && c_tri > 0 && c_tri >= c_tlas);
+        const bool run_tlas = !run_tri && (c_tlas >= VOTE || (no_inner && c_tlas > 0));
         if (run_tri)
         {
             if (is_tri)
