@@ -350,7 +350,7 @@ typedef enum SpkOption {
                                     CTA; 3162 / 3084 the same with the sort kept in pixel order inside a class; 2162 /
                                     2084 persistent pixel-pulling grid; 831 / 830 / 1621 / 461 phased kernel; 1 = plain
                                     per-pixel loop */
-    SPK_OPT_WAVEFRONT_SLOTS = 1, /* path slots of the wavefront tracer (default 2^24; 108 bytes each) */
+    SPK_OPT_WAVEFRONT_SLOTS = 1, /* path slots of the wavefront tracer (default 2^26, capped by the work of the call; 108 bytes each) */
     SPK_OPT_WAVEFRONT_CHUNK = 2, /* wavefront iterations queued per host read of the control block (default 8) */
     SPK_OPT_TRACE_VOTE = 3,      /* ray-batch kernel: lanes waiting in a leaf state that switch the warp to it (4, 6, 8, 12, 16; default 6) */
     SPK_OPT_SMEM_CARVEOUT = 4,   /* percent of the SM's shared-memory/L1 array asked for as shared memory; -1 driver

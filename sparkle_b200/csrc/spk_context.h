@@ -96,7 +96,7 @@ struct SpkContext
     int mega_variant = 1084; // megakernel form (SPK_OPT_MEGAKERNEL_FORM code) spk_cuda_choose_tracer measured fastest
     // explicit options (spk_cuda_set_option); nothing is read from the environment
     int opt_mega_form = 0;           // 0: use mega_variant
-    uint32_t opt_wf_slots = 1u << 24; // 16 Mi slots = 1.6 GB: city-10M at 4K gains 23 % over 1 Mi (launch tails)
+    uint32_t opt_wf_slots = 1u << 26; // 64 Mi slots = 7.2 GB (capped by the work of the call): fewer launch tails; city-10M at 4K x 32 spp: 4 / 8 / 16 / 32 / 64 Mi = 398 / 414 / 425 / 434 / 442 Mpaths/s
     uint32_t opt_wf_chunk = 8;
     uint32_t opt_wf_sort = 0; // wavefront ray sorting: bits per axis of the origin cell in the sort key (0 = off)
     int opt_vote = 6;
