@@ -110,7 +110,6 @@ __global__ void wf_init_kernel(WfState st, unsigned long long total)
     if (k < st.slots)
     {
         st.regen[k] = k;
-        st.rec[kRec * size_t(k)].w = __uint_as_float(kEmptySlot);
     }
     if (k == 0)
     {
@@ -156,8 +155,7 @@ __global__ void __launch_bounds__(kShadeThreads)
         const uint32_t slot = st.regen[k];
         if (k >= gen)
         {
-            st.rec[kRec * size_t(slot)].w = __uint_as_float(kEmptySlot); // no work left for this slot
-            continue;
+            continue; // no work left for this slot: it stays out of the queues from here on
         }
         // work item w = work_next + k = sample * W*H + pixel, without a 64-bit division per path
         uint32_t s = s0;
@@ -566,7 +564,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
     // ray sorting: three queue buffers rotate. The queue an iteration fills is sorted by ray key into the spare buffer,
     // which wf_extend and the next wf_shade read; the counts in the control block stay indexed by parity.
     uint32_t *q_cur = st.queue[0], *q_nxt = st.queue[1], *q_spare = sort.queue_spare;
-    uint32_t sort_items = slots; // entries the sort covers: all slots until the work runs out, then what is left
+    uint32_t sort_items = slots; // upper bound of a queue's length: all slots until the work runs out, then what is left
     WfCtrl h{};
     for (;; chunk = chunk_next)
     {
@@ -574,7 +572,10 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
         {
             st.queue[cur] = q_cur;
             st.queue[cur ^ 1u] = q_nxt;
-            wf_shade_kernel<<<slot_blocks, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur, ctx->d_accum);
+            // the grid covers what the queue can hold: all slots while new paths start, then (the queue only shrinks) its
+            // length at the host's last look
+            wf_shade_kernel<<<(sort_items + kShadeThreads - 1) / kShadeThreads, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur,
+                                                                                                         ctx->d_accum);
             wf_regen_kernel<<<regen_blocks, kShadeThreads, 0, s>>>(ctx->camera, a, st, cur ^ 1u);
             wf_advance_kernel<<<1, 1, 0, s>>>(st, cur, ctx->d_counters);
             ctx->stats.kernel_launches += 4;
