@@ -146,6 +146,15 @@ def test_wavefront_equals_megakernel(name, bounce, spp, oracle):
         assert np.allclose(wave, mega, rtol=2e-6, atol=1e-6), np.abs(wave - mega).max()
         assert st_w["paths"] == w * h * spp
         assert st_w["rays"] == st_m["rays"]  # the same paths, segment for segment
+    # SPK_OPT_WAVEFRONT_SORT: the ray queue sorted by origin cell + octant before it is traced; the same samples again
+    ctx.set_option(A.OPT_WAVEFRONT_SORT, 4)
+    ctx.reset_accumulation()
+    ctx.reset_stats()
+    ctx.render(first_sample=2, sample_count=spp, max_bounce=bounce, flags=A.FLAG_WAVEFRONT)
+    sorted_queue = ctx.resolve(A.RESOLVE_LINEAR_F32)
+    assert np.allclose(sorted_queue, mega, rtol=2e-6, atol=1e-6), np.abs(sorted_queue - mega).max()
+    assert ctx.stats()["rays"] == st_m["rays"]
+    ctx.set_option(A.OPT_WAVEFRONT_SORT, 0)
     ref, _ = oracle.render(desc, cam, w, h, first_sample=2, sample_count=spp, max_bounce=bounce)
     m = image_metrics(wave, ref / spp)
     if name == "room":
