@@ -138,6 +138,9 @@ def test_cube_map_sky_image(oracle):
         m["diag"] = dict(gpu_vs_port=float(np.abs(gpu - port / spp).mean()), ref_vs_port=float(np.abs(ref - port).mean() / spp),
                          gpu_again_vs_gpu=float(np.abs(again - gpu).mean()))
     assert m["mean_rel"] <= MEAN_REL_TOL and m["psnr"] > 40.0, m
+    # the wavefront tracer reads the same six faces (entries of the texture table): same samples, other summation order
+    wave, st_w = gpu_render(desc, cam, w, h, 0, spp, 8, flags=A.FLAG_WAVEFRONT)
+    assert np.allclose(wave, gpu, rtol=2e-6, atol=1e-6), np.abs(wave - gpu).max()
     # the committed golden image of the same scene (the pin that travels)
     import os
     golden = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.npz"))
