@@ -71,6 +71,12 @@ int orc_kat_camera(const float *center, float radius, float pitch_deg, float yaw
                    float sensor_height, float aperture, float exposure, uint32_t width, uint32_t height, SpkCamera *out);
 /* GLTFLoader::ProcessNode transform of a root-level node (GLTFLoader.cpp:532-544): translation, rotation xyzw */
 int orc_kat_gltf_node(const float *translation, const float *rotation_xyzw, float *fwd12, float *inv12);
+/* reference build only: Image2D::LoadFromFile's HDR branch (stbi_loadf, clamp, half; Image.cpp:152-181) on a file image in
+ * memory, and the loop of SkyLightCookJob::Execute (SkyLight.cpp:103-118) at a given cube size */
+int orc_kat_decode_hdr(const unsigned char *data, uint32_t size, uint32_t *width, uint32_t *height, uint16_t *rgba_half,
+                       uint64_t capacity_halves);
+int orc_kat_cook_sky_cube(const uint16_t *equirect_rgba_half, uint32_t width, uint32_t height, uint32_t size,
+                          uint16_t *faces_out);
 /* "port" only: 0 = glibc float sin/cos/pow as the reference calls them (default), 1 = evaluated in double and rounded
  * once, as the CUDA path does (separates operation-order parity from one-ulp libm drift; oracle.cpp g_libm_mode) */
 int orc_set_libm(uint32_t mode);

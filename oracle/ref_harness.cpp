@@ -74,6 +74,7 @@
 #undef private
 #undef protected
 
+#include <stb_image.h> // declarations only: Image.cpp holds the implementation
 #include "oracle.h"
 
 using namespace sparkle;
@@ -987,5 +988,63 @@ int orc_resolve(const float *accum, uint32_t width, uint32_t height, uint32_t ac
     renderer.ToneMappingPass(renderer.output_image_); // CPURenderer.cpp:565-576
     memcpy(out, renderer.output_image_.GetRawData(), size_t(width) * height * 8);
     return SPK_OK;
+}
+
+// ---- the sky map of a SkyLight (pins sparkle_b200/host/sky_cook.cpp): the reference's own functions, called the way
+// Image2D::LoadFromFile (io/Image.cpp:152-181) and SkyLightCookJob::Execute (scene/component/light/SkyLight.cpp:103-118) do
+int orc_kat_decode_hdr(const unsigned char *data, uint32_t size, uint32_t *width, uint32_t *height, uint16_t *rgba_half,
+                       uint64_t capacity_halves)
+{
+    if (!stbi_is_hdr_from_memory(data, int(size)))
+    {
+        return -1;
+    }
+    int w = 0, h = 0, channels = 0;
+    float *px = stbi_loadf_from_memory(data, int(size), &w, &h, &channels, 4);
+    if (!px)
+    {
+        return -2;
+    }
+    *width = uint32_t(w);
+    *height = uint32_t(h);
+    if (uint64_t(w) * uint64_t(h) * 4 > capacity_halves)
+    {
+        stbi_image_free(px);
+        return -3;
+    }
+    const float half_max = static_cast<float>(std::numeric_limits<Half>::max());
+    for (size_t k = 0; k < size_t(w) * size_t(h) * 4; k++)
+    {
+        const Half v = static_cast<Half>(std::clamp(px[k], -half_max, half_max));
+        memcpy(rgba_half + k, &v, 2);
+    }
+    stbi_image_free(px);
+    return 0;
+}
+
+int orc_kat_cook_sky_cube(const uint16_t *equirect_rgba_half, uint32_t width, uint32_t height, uint32_t size, uint16_t *faces_out)
+{
+    Image2D sky_map(width, height, PixelFormat::RGBAFloat16);
+    memcpy(const_cast<uint8_t *>(sky_map.GetRawData()), equirect_rgba_half, size_t(width) * height * 8);
+    Image2DCube cube_map(size, size, PixelFormat::RGBAFloat16, "kat_CubeMap");
+    for (unsigned id = 0; id < Image2DCube::FaceId::Count; id++)
+    {
+        auto face_id = static_cast<Image2DCube::FaceId>(id);
+        auto &this_face = cube_map.GetFace(face_id);
+        for (unsigned i = 0; i < size; i++)
+        {
+            for (unsigned j = 0; j < size; j++)
+            {
+                auto u = (static_cast<Scalar>(i) + 0.5f) / static_cast<Scalar>(size) * 2.f - 1.f;
+                auto v = (static_cast<Scalar>(j) + 0.5f) / static_cast<Scalar>(size) * 2.f - 1.f;
+                Vector3 direction = Image2DCube::TextureCoordinateToDirection(face_id, u, v);
+                Vector2 eq_uv = utilities::CartesianToEquirectangular(direction);
+                Vector3 color = sky_map.Sample(eq_uv);
+                this_face.SetPixel(i, j, color);
+            }
+        }
+        memcpy(faces_out + size_t(id) * size * size * 4, this_face.GetRawData(), size_t(size) * size * 8);
+    }
+    return 0;
 }
 } // extern "C"

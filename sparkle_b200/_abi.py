@@ -173,6 +173,9 @@ HOST_SYMBOLS = {
     "spk_host_scene_desc": (C.POINTER(SceneDesc), [C.c_void_p]),
     "spk_host_scene_free": (None, [C.c_void_p]),
     "spk_host_usd_probe": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint64)]),
+    "spk_host_decode_hdr": (C.c_int, [C.c_char_p, C.c_size_t, u32p, u32p, C.POINTER(C.c_void_p)]),
+    "spk_host_free_buffer": (None, [C.c_void_p]),
+    "spk_host_cook_sky_cube": (C.c_int, [C.c_void_p, u32, u32, u32, C.c_void_p]),
     "spk_host_scene_load_usd": (C.c_void_p, [C.c_char_p, u32, u32]),
     "spk_host_scene_camera": (C.POINTER(Camera), [C.c_void_p]),
     "spk_host_gltf_probe": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_uint64)]),

@@ -4,6 +4,7 @@
  * renderer fails to initialise, logs, and CreateRenderer returns nullptr (AppFramework.cpp:200-205 convention).
  */
 #include "cuda_renderer.h"
+#include "sky_cook.h"
 #include "ref_math.h"
 
 #include <algorithm>
@@ -11,6 +12,8 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <fstream>
+#include <iterator>
 #include <sstream>
 
 #include "bvh_builder.h"
@@ -356,6 +359,8 @@ struct SceneProxy::Impl
     SpkHostBvh *tlas = nullptr;
     bool has_sky = false;
     Vec3 sky_color{0.5f, 0.7f, 1.0f}; // SkyLight.h:101
+    std::vector<uint16_t> sky_faces; // cooked sky map: 6 faces of sky_face_size^2 RGBAFloat16 pixels, else empty
+    uint32_t sky_face_size = 0;
     ~Impl()
     {
         for (auto &m : meshes)
@@ -538,6 +543,31 @@ void SceneProxy::SetSky(Vec3 color)
     impl_->sky_color = color;
 }
 
+bool SceneProxy::SetSkyMapFile(const std::string &hdr_path, uint32_t cube_size)
+{
+    std::ifstream in(hdr_path, std::ios::binary);
+    if (!in)
+    {
+        SetLastError("SkyLight: failed to read image file " + hdr_path);
+        return false;
+    }
+    std::vector<uint8_t> bytes((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+    uint32_t w = 0, h = 0;
+    std::vector<uint16_t> equirect;
+    std::string error;
+    if (!DecodeRadianceHdr(bytes.data(), bytes.size(), w, h, equirect, error))
+    {
+        SetLastError("SkyLight: failed to decode image " + hdr_path + ": " + error);
+        return false;
+    }
+    const uint32_t size = cube_size ? cube_size : kSkyCubeSize;
+    impl_->sky_faces.assign(size_t(6) * size * size * 4, 0);
+    CookSkyCube(equirect.data(), w, h, size, impl_->sky_faces.data());
+    impl_->sky_face_size = size;
+    impl_->has_sky = true;
+    return true;
+}
+
 void SceneProxy::RebuildDesc(bool structural)
 {
     if (structural)
@@ -596,6 +626,13 @@ void SceneProxy::RebuildDesc(bool structural)
     desc_.sky.color[0] = impl_->sky_color.x;
     desc_.sky.color[1] = impl_->sky_color.y;
     desc_.sky.color[2] = impl_->sky_color.z;
+    desc_.sky.has_map = impl_->sky_faces.empty() ? 0u : 1u;
+    for (uint32_t f = 0; f < 6 && desc_.sky.has_map; f++)
+    {
+        const size_t face_halves = size_t(impl_->sky_face_size) * impl_->sky_face_size * 4;
+        desc_.sky.faces[f] = SpkTextureDesc{impl_->sky_faces.data() + f * face_halves, impl_->sky_face_size, impl_->sky_face_size,
+                                            SPK_FMT_RGBA16F, 0};
+    }
     desc_.world_extent = extent;
 }
 

@@ -164,6 +164,9 @@ public:
     uint32_t AddSphere(Vec3 center, float radius, uint32_t material); // SpherePrimitive.cpp:22-38
     void MovePrimitive(uint32_t primitive, const Transform &t);       // records PrimitiveChangeType::Update
     void SetSky(Vec3 color);
+    // SkyLight::SetSkyMap (SkyLight.cpp): an equirectangular Radiance .hdr file, cooked into the 6 x 1024 x 1024 RGBAFloat16
+    // cube the path tracer samples (host/sky_cook.h). False (and LastError) when the file cannot be read or decoded.
+    bool SetSkyMapFile(const std::string &hdr_path, uint32_t cube_size = 0 /* 0: the reference's 1024 */);
     CameraProxy &GetCamera() { return camera_; }
 
     // SceneRenderProxy::Update/UpdateBVH: (re)build the TLAS when the change list is not empty; returns the changes of

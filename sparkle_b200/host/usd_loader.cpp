@@ -995,8 +995,11 @@ struct Converter
                 const UsdProperty *file = c->Prop("inputs:texture:file");
                 if (file && file->value.has_text && !file->value.text.empty())
                 {
-                    SetLastError("USDLoader: sky map " + file->value.text +
-                                 " ignored (no HDR decoder in this build): the dome light's colour is used");
+                    // the texture path is relative to the USD file (USDLoader.cpp:490-493); SkyLight::SetSkyMap cooks it
+                    if (!scene.SetSkyMapFile(dir.empty() ? file->value.text : dir + "/" + file->value.text))
+                    {
+                        return false;
+                    }
                 }
                 stats.dome_lights++;
             }

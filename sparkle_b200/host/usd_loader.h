@@ -14,8 +14,9 @@
  *     dielectric with eta = ior; diffuseColor / emissiveColor / normal / metallic+roughness are constants or
  *     `UsdUVTexture` connections (one packed metallic-roughness image read through .g / .b); an emissive texture forces
  *     emissive_color = 1; colour images are sRGB when inputs:sourceColorSpace = "sRGB", else Unorm (:195-205)
- *   - `DomeLight` -> sky colour = color * intensity * 2^exposure (:455-458); a sky MAP (inputs:texture:file, an .hdr
- *     file) needs an HDR decoder and cube conversion that are not built: the colour is used and an error is logged
+ *   - `DomeLight` -> sky colour = color * intensity * 2^exposure (:455-458); a sky MAP (inputs:texture:file, an
+ *     equirectangular Radiance .hdr next to the .usda, :490-493) is decoded and cooked into the 6 x 1024^2 RGBAFloat16
+ *     cube of SkyLightCookJob (host/sky_cook.h), which the path tracer then samples instead of the colour
  *   - `Camera` -> orbit camera rebuilt from the node transform and focusDistance (OrbitCameraComponent.cpp:32-56; lens
  *     attributes in millimetres, USDLoader.cpp:95-116); `DistantLight` is read and ignored (the path tracers light
  *     with the sky and emissive surfaces only)

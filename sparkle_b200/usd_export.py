@@ -49,9 +49,11 @@ def _valid(name):
     return "_" + out if out[0].isdigit() else out
 
 
-def write_usda(sb, path, camera=None, width=None, height=None):
+def write_usda(sb, path, camera=None, width=None, height=None, sky_hdr=None):
     """sb: SceneBuilder (before or after finalize). camera: dict(center, radius, pitch, yaw[, focal_length,
-    sensor_height, aperture]) or None. Returns the .usda path."""
+    sensor_height, aperture]) or None. sky_hdr: (file name, bytes of an equirectangular Radiance .hdr) written next to the
+    textures and referenced by the dome light like USDExporter.cpp:449-463 does for a SkyLight with a sky map. Returns the
+    .usda path."""
     path = str(path)
     out_dir = os.path.dirname(path)
     os.makedirs(os.path.join(out_dir, "textures"), exist_ok=True)
@@ -119,12 +121,18 @@ def write_usda(sb, path, camera=None, width=None, height=None):
               f"            float focusDistance = {_fmt(radius)}", f"            float fStop = {_fmt(camera.get('aperture', 22.0))}",
               '            token projection = "perspective"',
               f"            float verticalAperture = {_fmt(camera.get('sensor_height', 0.024) * 1000.0)}", "        }", "    }", ""]
-    if sb.sky.get("has_sky"):
-        c = sb.sky["color"]
+    if sb.sky.get("has_sky") or sky_hdr:
+        c = sb.sky.get("color", (1.0, 1.0, 1.0))
+        dome = [f"            color3f inputs:color = ({_fmt(c[0])}, {_fmt(c[1])}, {_fmt(c[2])})",
+                "            float inputs:intensity = 1"]
+        if sky_hdr:
+            name, data = sky_hdr
+            with open(os.path.join(out_dir, "textures", name), "wb") as fh:
+                fh.write(data)
+            dome.append(f"            asset inputs:texture:file = @textures/{name}@")
         L += ['    def Xform "sky_node"', "    {", "        matrix4d xformOp:transform = " + _matrix(np.eye(4)[:3]),
-              '        uniform token[] xformOpOrder = ["xformOp:transform"]', "", '        def DomeLight "sky"', "        {",
-              f"            color3f inputs:color = ({_fmt(c[0])}, {_fmt(c[1])}, {_fmt(c[2])})",
-              "            float inputs:intensity = 1", "        }", "    }", ""]
+              '        uniform token[] xformOpOrder = ["xformOp:transform"]', "", '        def DomeLight "sky"', "        {"]
+        L += dome + ["        }", "    }", ""]
     L += ["}", "", 'def Scope "_materials"', "{"]
     for mid, name in used_materials.items():
         m = sb.materials[mid]

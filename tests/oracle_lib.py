@@ -56,6 +56,8 @@ def load(kind="reference"):
         lib.orc_kat_transform.argtypes = [fp, fp, fp, fp, fp]
         lib.orc_kat_gltf_node.argtypes = [fp, fp, fp, fp]
         lib.orc_kat_camera.argtypes = [fp, f32, f32, f32, f32, f32, f32, f32, u32, u32, C.POINTER(A.Camera)]
+        lib.orc_kat_decode_hdr.argtypes = [C.c_char_p, u32, C.POINTER(u32), C.POINTER(u32), C.c_void_p, C.c_uint64]
+        lib.orc_kat_cook_sky_cube.argtypes = [C.c_void_p, u32, u32, u32, C.c_void_p]
     else:
         lib.orc_set_libm.argtypes = [u32]
     _cache[kind] = lib
@@ -115,6 +117,22 @@ class Oracle:
         fwd, inv = np.zeros(12, np.float32), np.zeros(12, np.float32)
         self.lib.orc_kat_gltf_node(*[a.ctypes.data_as(A.fp) for a in (t, q, fwd, inv)])
         return fwd.reshape(3, 4), inv.reshape(3, 4)
+
+    def kat_decode_hdr(self, data):
+        """Image2D::LoadFromFile's HDR branch on a file image: (h, w, 4) uint16 half bits, or None when stb refuses it"""
+        w, h = A.u32(0), A.u32(0)
+        buf = np.zeros(1 << 24, np.uint16)
+        rc = self.lib.orc_kat_decode_hdr(data, len(data), C.byref(w), C.byref(h), buf.ctypes.data, buf.size)
+        if rc != 0:
+            return None
+        return buf[: w.value * h.value * 4].reshape(h.value, w.value, 4).copy()
+
+    def kat_cook_sky_cube(self, equirect_half, size):
+        """SkyLightCookJob::Execute's loop: (6, size, size, 4) uint16 half bits"""
+        eq = np.ascontiguousarray(equirect_half, np.uint16)
+        faces = np.zeros((6, size, size, 4), np.uint16)
+        self.lib.orc_kat_cook_sky_cube(eq.ctypes.data, eq.shape[1], eq.shape[0], size, faces.ctypes.data)
+        return faces
 
     def kat_camera(self, width, height, center=(0, 0, 0), radius=25.0, pitch=10.0, yaw=-20.0, focal_length=0.035,
                    sensor_height=0.024, aperture=22.0, exposure=1.0):

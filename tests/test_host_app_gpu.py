@@ -175,3 +175,30 @@ def test_usd_scene_through_the_host_app(tmp_path, oracle):
     for f in ("position", "front", "max_u", "max_v", "lower_left"):
         assert np.allclose(list(getattr(a.camera, f)), list(getattr(pcam, f)), rtol=1e-5, atol=2e-5), f
     a.close()
+
+
+def test_usd_scene_with_a_sky_map_through_the_host_app(tmp_path, oracle):
+    """DomeLight with inputs:texture:file: the .hdr is cooked into the cube on the host (host/sky_cook.cpp, bit-equal to the
+    reference's SkyLightCookJob in tests/test_sky_cook_cpu.py) and the path tracer lights the scene with it; the image
+    equals the CPU path tracer's on the app's own scene description."""
+    import hdr_files as H
+    from sparkle_b200 import usd_export
+    sb, camkw = scenes.testscene(models=False)
+    data = H.write_hdr(H.float_to_rgbe(H.make_sky()))
+    path = usd_export.write_usda(sb, tmp_path / "sky.usda", camera=camkw, sky_hdr=("sky.hdr", data))
+    w, h, spp = 96, 64, 4
+    a = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 2 --spatial_denoise false "
+                    f"--scene {path}")
+    a.run()
+    assert a.cumulated_samples == spp and a.scene.sky.has_map == 1 and a.scene.sky.faces[0].width == 1024
+    gpu = a.read_linear()
+    ref, _ = oracle.render(a.scene, a.camera, w, h, 0, spp, accum_mode=A.ACCUM_RUNNING_AVERAGE)
+    assert rel_err(gpu, ref) <= 1e-3
+    # the map lights the scene: the same file without it (gradient sky of the dome light's colour) is another image
+    plain = usd_export.write_usda(sb, tmp_path / "plain.usda", camera=camkw)
+    b = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 2 --spatial_denoise false "
+                    f"--scene {plain}")
+    b.run()
+    assert rel_err(b.read_linear(), ref) > 0.05
+    a.close()
+    b.close()

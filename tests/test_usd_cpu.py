@@ -209,3 +209,39 @@ def Xform "World" (
     assert m.type == A.MAT_PBR and list(m.base_color) == [0.25, 0.5, 0.75]
     assert np.float32(m.metallic) == 0 and np.float32(m.roughness) == np.float32(0.5)
     A.host_lib().spk_host_scene_free(s)
+
+
+def test_dome_light_with_a_sky_map(tmp_path):
+    """DomeLight inputs:texture:file: the .hdr next to the .usda is decoded and cooked into the 6 x 1024^2 RGBAFloat16 cube
+    (SkyLight::SetSkyMap -> SkyLightCookJob); the scene description carries the faces (has_map)."""
+    import hdr_files as H
+    sb, camkw = scenes.testscene(models=False)
+    data = H.write_hdr(H.float_to_rgbe(H.make_sky()))
+    path = usd_export.write_usda(sb, tmp_path / "sky.usda", camera=camkw, sky_hdr=("sky.hdr", data))
+    s, desc, _ = load(path)
+    assert desc.sky.has_sky == 1 and desc.sky.has_map == 1
+    faces = []
+    for f in range(6):
+        t = desc.sky.faces[f]
+        assert (t.width, t.height, t.format) == (1024, 1024, A.FMT_RGBA16F)
+        faces.append(np.ctypeslib.as_array(C.cast(t.pixels, C.POINTER(C.c_uint16)), (1024, 1024, 4)).copy())
+    faces = np.stack(faces)
+    # the same cube through the cook entry point, and through the reference's own functions where they are built
+    lib = A.host_lib()
+    w, h, p = A.u32(0), A.u32(0), C.c_void_p()
+    assert lib.spk_host_decode_hdr(data, len(data), C.byref(w), C.byref(h), C.byref(p)) == 0
+    eq = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint16)), (h.value, w.value, 4)).copy()
+    lib.spk_host_free_buffer(p)
+    again = np.zeros_like(faces)
+    assert lib.spk_host_cook_sky_cube(eq.ctypes.data, w.value, h.value, 1024, again.ctypes.data) == 0
+    assert np.array_equal(faces, again)
+    if O.available("reference"):
+        assert np.array_equal(faces, O.Oracle("reference").kat_cook_sky_cube(eq, 1024))
+    lib.spk_host_scene_free(s)
+    # a missing or broken file fails the load, loudly
+    os.remove(tmp_path / "textures" / "sky.hdr")
+    with pytest.raises(RuntimeError, match="sky.hdr"):
+        load(path)
+    (tmp_path / "textures" / "sky.hdr").write_bytes(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n+Y 4 +X 4\n" + bytes(64))
+    with pytest.raises(RuntimeError, match="decode"):
+        load(path)
