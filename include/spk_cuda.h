@@ -297,6 +297,11 @@ int spk_cuda_resolve(SpkContext *ctx, uint32_t format, uint32_t total_samples, v
 int spk_cuda_accum_device_ptr(SpkContext *ctx, void **device_ptr, size_t *bytes);
 int spk_cuda_accum_sample_count(SpkContext *ctx, uint32_t *count);
 
+/* Parity probe: the device's sinf (op 0) / cosf (1) / powf (2, with y) on host arrays. The reference calls std::sin, std::cos
+ * and std::pow on floats, i.e. glibc's float routines (sysdeps/ieee754/flt-32/s_sinf.c, s_cosf.c, e_powf.c); the device
+ * restates them (csrc/spk_glibc_math.cuh) and this entry point lets a test compare the two argument by argument. */
+int spk_cuda_probe_libm(SpkContext *ctx, uint32_t op, const float *x, const float *y, uint64_t n, float *out);
+
 /* SceneRenderProxy::Intersect<false> on a ray batch (SceneRenderProxy.cpp:82-126, 299-312), host buffers:
  * H2D of rays, traversal, D2H of hits inside the call. */
 int spk_cuda_trace_closest(SpkContext *ctx, const SpkRay *rays, uint64_t num_rays, SpkHit *hits, uint32_t flags);

@@ -41,16 +41,23 @@ constexpr float kTolerance = 1e-4f;
 constexpr float kPi = 3.14159274101257324f;        // std::numbers::pi_v<float>
 
 // libm mode (orc_set_libm, port only). 0 = glibc's float routines, what the reference calls (default; every parity pin
-// against the reference uses it). 1 = "device libm": sin, cos and pow evaluated in double and rounded once to float, which
-// is what the CUDA path does (spk_shade.cuh ref_sincos / ref_pow / ref_pow5). The two differ by one ulp for ~1 % of
-// arguments; mode 1 lets a test separate "the GPU follows the reference's operation order" (GPU == port in mode 1, to
-// accumulation rounding) from "how far one-ulp libm differences move an image" (port mode 1 vs reference, CPU only).
+// against the reference uses it). 1 = "device libm": what the CUDA path computes. Since the device restates glibc's sinf /
+// cosf / powf (csrc/spk_glibc_math.cuh) the only difference left is Schlick's (1 - cos)^5, which the device evaluates as an
+// exact product in double rounded once (spk_shade.cuh ref_pow5) where the reference calls std::pow(x, 5.f): one ulp apart
+// for ~0.1 % of the arguments. Mode 1 lets a test separate "the GPU follows the reference's operation order" (GPU == port
+// in mode 1, to accumulation rounding) from that share (port mode 1 vs reference, CPU only). (Until late in round 2 the
+// device evaluated sin, cos and pow in double and rounded once, and mode 1 did the same.)
 int g_libm_mode = 0;
-inline float m_sin(float x) { return g_libm_mode ? static_cast<float>(std::sin(static_cast<double>(x))) : std::sin(x); }
-inline float m_cos(float x) { return g_libm_mode ? static_cast<float>(std::cos(static_cast<double>(x))) : std::cos(x); }
+inline float m_sin(float x) { return std::sin(x); }
+inline float m_cos(float x) { return std::cos(x); }
 inline float m_pow(float x, float y)
 {
-    return g_libm_mode ? static_cast<float>(std::pow(static_cast<double>(x), static_cast<double>(y))) : std::pow(x, y);
+    if (g_libm_mode && y == 5.f)
+    {
+        const double d = static_cast<double>(x), d2 = d * d;
+        return static_cast<float>(d2 * d2 * d);
+    }
+    return std::pow(x, y);
 }
 constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<float>
 

@@ -130,6 +130,7 @@ CUDA_SYMBOLS = {
     "spk_cuda_choose_tracer": (C.c_int, [CtxP, u32, C.POINTER(u32), C.POINTER(C.c_float)]),
     "spk_cuda_accum_device_ptr": (C.c_int, [CtxP, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "spk_cuda_accum_sample_count": (C.c_int, [CtxP, u32p]),
+    "spk_cuda_probe_libm": (C.c_int, [CtxP, u32, C.c_void_p, C.c_void_p, u64, C.c_void_p]),
     "spk_cuda_trace_closest": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
     "spk_cuda_trace_closest_device": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),
     "spk_cuda_trace_closest_noalloc": (C.c_int, [CtxP, C.c_void_p, u64, C.c_void_p, u32]),

@@ -882,6 +882,25 @@ __device__ __forceinline__ float aces(float c)
     return fminf(fmaxf(r, 0.f), 1.f);
 }
 
+__global__ void probe_libm_kernel(uint32_t op, const float *__restrict__ x, const float *__restrict__ y, uint64_t n,
+                                  float *__restrict__ out)
+{
+    const uint64_t k = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k < n)
+    {
+        float s, c;
+        if (op == 2u)
+        {
+            out[k] = ref_pow(x[k], y[k]);
+        }
+        else
+        {
+            ref_sincos(x[k], &s, &c);
+            out[k] = op == 0u ? s : c;
+        }
+    }
+}
+
 __global__ void resolve_kernel(const float4 *__restrict__ accum, uint32_t width, uint32_t height, uint32_t format,
                                float divisor, float exposure, void *__restrict__ out)
 {
@@ -1388,6 +1407,48 @@ int spk_cuda_tracer_choice(SpkContext *ctx, int32_t *wavefront_out, uint32_t *me
     }
     *wavefront_out = ctx->tracer_choice;
     *megakernel_form_out = (uint32_t)ctx->mega_variant;
+    return SPK_OK;
+}
+
+// parity probe: the device's sin / cos / pow on host arrays (tests/test_libm_gpu.py compares them with the host's libm)
+int spk_cuda_probe_libm(SpkContext *ctx, uint32_t op, const float *x, const float *y, uint64_t n, float *out)
+{
+    if (!ctx || !x || !out || op > 2u || (op == 2u && !y) || n > (1ull << 28))
+    {
+        set_error("spk_cuda_probe_libm: invalid argument");
+        return SPK_ERR_INVALID_ARGUMENT;
+    }
+    if (n == 0)
+    {
+        return SPK_OK;
+    }
+    SPK_CUDA_TRY(cudaSetDevice(ctx->device));
+    float *d = nullptr;
+    SPK_CUDA_TRY(cudaMalloc(&d, size_t(n) * 3 * sizeof(float)));
+    cudaError_t e = cudaMemcpyAsync(d, x, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && op == 2u)
+    {
+        e = cudaMemcpyAsync(d + n, y, n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (e == cudaSuccess)
+    {
+        probe_libm_kernel<<<unsigned((n + 255) / 256), 256, 0, ctx->stream>>>(op, d, d + n, n, d + 2 * n);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaMemcpyAsync(out, d + 2 * n, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess)
+    {
+        e = cudaStreamSynchronize(ctx->stream);
+    }
+    cudaFree(d);
+    if (e != cudaSuccess)
+    {
+        set_error(std::string("spk_cuda_probe_libm: ") + cudaGetErrorString(e));
+        return SPK_ERR_CUDA;
+    }
     return SPK_OK;
 }
 

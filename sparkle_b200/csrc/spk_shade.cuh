@@ -10,13 +10,13 @@
  *   BxDFs          scene/material/BxDF.h:32-141, DistributionVn (Sampler.h:133-165), Utilities.h:201-324,434-451
  *   sky            SkyRenderProxy::Evaluate (SkyRenderProxy.cpp:50-64), Image2DCube (io/Image.cpp:298-357)
  *
- * libm: sqrt and division are IEEE on the device. sin, cos and pow are evaluated in double and rounded once to float;
- * glibc's float routines are within 0.56 ulp, so the two agree except for 1.3 % (sin, cos) / 0.07 % (pow) of arguments
- * where they differ by one ulp (measured against the box's libm). A one-ulp difference moves a path
- * continuously (~1e-7 relative); only a random number within an ulp of a branch threshold changes a decision.
+ * libm: sqrt and division are IEEE on the device. sin, cos and pow are glibc's own algorithms (spk_glibc_math.cuh): bit-equal
+ * to the libm the reference runs on. (Rounds 1 and 2 evaluated them in double and rounded once, which differs from glibc by
+ * one ulp for 1.3 % of the sin / cos and 0.07 % of the pow arguments.)
  */
 #pragma once
 #include "spk_device.cuh"
+#include "spk_glibc_math.cuh"
 
 #include <cuda_fp16.h>
 
@@ -27,28 +27,19 @@ constexpr float kTolerance = 1e-4f;
 constexpr float kPi = 3.14159274101257324f;      // std::numbers::pi_v<float>
 constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<float>
 
-// One out-of-line copy each: the double-precision bodies are 100-500 instructions and were inlined at every call site
-// (three sin/cos pairs, fourteen pow), most of a 108 KiB kernel against a 32 KiB instruction cache.
-static __device__ __noinline__ void ref_sincos(float x, float *s, float *c)
+// sin, cos and pow are glibc's float routines restated on the device (spk_glibc_math.cuh): the same float for the same
+// argument as the reference's std::sin / std::cos / std::pow. One out-of-line copy each (three sin/cos pairs and fourteen
+// pow call sites would otherwise be inlined into every kernel).
+static __device__ __forceinline__ void ref_sincos(float x, float *s, float *c)
 {
-    double ds, dc;
-    sincos((double)x, &ds, &dc); // same values as sin() and cos(): both are correctly rounded to < 1 ulp in double
-    *s = (float)ds;
-    *c = (float)dc;
+    glibc_sincosf(x, s, c);
 }
-// x > 0 (every call site: sRGB decode and encode of values in (0, 1]): exp(y * log(x)) in double. log and exp are each
-// within 1 ulp of double, the product adds ~1e-15 absolute, so the result is within ~4e-15 relative of x^y before the one
-// rounding to float — the same float as the full double pow except when x^y lies within 4e-15 of a rounding boundary
-// (probability ~1e-7 per call), at a third of the instructions of pow()'s extended-precision path.
-static __device__ __noinline__ float ref_pow(float x, float y)
+static __device__ __forceinline__ float ref_pow(float x, float y)
 {
-    if (x > 0.f)
-    {
-        return (float)exp((double)y * log((double)x));
-    }
-    return (float)pow((double)x, (double)y);
+    return glibc_powf(x, y);
 }
-// std::pow(x, 5.f): exact product in double, one rounding
+// std::pow(x, 5.f) of Schlick's approximation: the exact product in double, rounded once (glibc's powf agrees except for
+// ~0.1 % of the arguments, by one ulp, in a factor no branch depends on; the full routine would cost 10x as much here)
 __device__ __forceinline__ float ref_pow5(float x)
 {
     double d = (double)x, d2 = d * d;

@@ -216,8 +216,9 @@ def test_running_average_cap_port_equals_reference(port):
 
 
 def test_device_libm_mode_of_the_port(port):
-    """orc_set_libm(1): sin/cos/pow in double, rounded once (what the CUDA path computes). Differs from glibc's float
-    routines by at most one ulp, on a small share of arguments; mode 0 restores the reference's bits."""
+    """orc_set_libm(1): what the CUDA path computes: glibc's sin / cos / pow like the reference, except Schlick's
+    (1 - cos)^5 as an exact product rounded once (one ulp from std::pow(x, 5.f) for ~0.1 % of the arguments); mode 0
+    restores the reference's bits."""
     x = np.random.default_rng(5).uniform(0, 6.3, 20000).astype(np.float32)
     base = np.array([port.kat_libm(0, v) for v in x[:2000]])
     sb, camkw = scenes.testscene()
@@ -232,5 +233,5 @@ def test_device_libm_mode_of_the_port(port):
     again, _ = port.render(desc, cam, 48, 32, 0, 4, threads=2)
     assert_same_bits(again, plain, "mode 0 restored")
     rel = np.abs(dev[..., :3] - plain[..., :3]).sum(-1) / np.maximum(plain[..., :3].sum(-1), 1e-3)
-    assert rel.mean() < 1e-3 and (dev != plain).any(), rel.mean()
+    assert rel.mean() < 1e-5, rel.mean()
     assert np.array_equal(base, np.array([port.kat_libm(0, v) for v in x[:2000]]))
