@@ -13,7 +13,8 @@
  * each for sin, cos (0..2 pi and +-100), pow(x, 2.4), pow(x, 0.45); without the contractions 24 and 2 in 5e7 differ.
  * tests/test_libm_gpu.py checks the device functions against the same libm, argument by argument.
  * Tables: spk_glibc_tables.h (read out of the image's libm.so.6 by tools/gen_glibc_tables.py).
- * It is also cheaper than CUDA's double sincos() / exp(log()): ~25 double operations per call instead of 100-500.
+ * It is also cheaper than CUDA's double sincos() / exp(log()) once written branch-free with immediate coefficients and
+ * without calls into CUDA's double routines (measured steps in DESIGN.md 3): TestScene 32.73 -> 32.08 ms per 64 spp.
  */
 #pragma once
 #include "spk_glibc_tables.h"
@@ -24,68 +25,66 @@ namespace glibc
 {
 __device__ __forceinline__ unsigned abstop12(float x) { return (__float_as_uint(x) >> 20) & 0x7ffu; }
 
-// __sincosf_table entry: sign[4], hpi_inv, hpi, c0, c1, s1, c2, s2, c3, s3, c4
-// sinf_poly (sincosf.h): sine for even n, cosine for odd n
-__device__ __forceinline__ float sinf_poly(double x, double x2, const double *p, int n)
+// sinf / cosf / sincosf for |y| < 120 (s_sinf.c, s_cosf.c, sincosf.h), branch-free: lanes of a warp fall into different
+// quadrants and argument ranges, and a literal transcription runs the sine and the cosine polynomial for each of them in
+// turn. What the three routines compute is the same two polynomials:
+//   reduce_fast: n = round(y * 2/pi) (through the 2^24-scaled product and an arithmetic shift), x = y - n * pi/2; for
+//                |y| < pi/4 it gives n = 0 and x = y exactly, which is the routines' separate small-argument branch
+//   sinf_poly:   S = x s + (x s)^3 s1 + (x s)^5 (s2 + x^2 s3)   with s = sign[n & 3] = {1, -1, -1, 1}
+//                C = (c0 + x^2 c1) + x^4 c2 + x^6 (c3 + x^2 c4)
+//   __sincosf_table[1] (quadrants 2, 3) is table [0] with the cosine coefficients negated: every term of C is linear in them
+//   and rounding is symmetric, so C's value is exactly negated
+//   sin y = n odd ? C : S, cos y = n odd ? S : C; below 2^-12 sin y = y and cos y = 1
+// Coefficients are immediates (a table in global memory put a trip to L1 in front of every polynomial: TestScene -25 %).
+__device__ __forceinline__ void sincos_fast(float y, float &sin_out, float &cos_out)
 {
-    if ((n & 1) == 0)
-    {
-        const double x3 = x * x2;
-        const double s1 = fma(x2, __ldg(p + 12), __ldg(p + 10));
-        const double x7 = x3 * x2;
-        const double s = fma(x3, __ldg(p + 8), x);
-        return (float)fma(x7, s1, s);
-    }
+    const double x0 = (double)y;
+    const double r = x0 * 0x1.45f306dc9c883p+23; // hpi_inv = 2 / pi * 2^24
+    const int n = (__double2int_rz(r) + 0x800000) >> 24;
+    const double x = fma(-(double)n, 0x1.921fb54442d18p+0, x0);
+    const double xs = ((n + 1) & 2) ? -x : x;
+    const double x2 = x * x;
+    // sine polynomial
+    const double x3 = xs * x2;
+    const double s1 = fma(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7); // s2 + x2 s3
+    const double x5 = x3 * x2;
+    const double s = fma(x3, -0x1.555545995a603p-3, xs); // x + x3 s1
+    const float S = (float)fma(x5, s1, s);
+    // cosine polynomial
     const double x4 = x2 * x2;
-    const double c2 = fma(x2, __ldg(p + 13), __ldg(p + 11));
-    const double c1 = fma(x2, __ldg(p + 7), __ldg(p + 6));
+    const double c2 = fma(x2, 0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10); // c3 + x2 c4
+    const double c1 = fma(x2, -0x1.ffffffd0c621cp-2, 1.0);                    // c0 + x2 c1
     const double x6 = x4 * x2;
-    const double c = fma(x4, __ldg(p + 9), c1);
-    return (float)fma(x6, c2, c);
-}
-
-// reduce_fast (sincosf.h): |x| < 120; hpi_inv is 2 / pi * 2^24, so the quadrant ends up in bits 24..31
-__device__ __forceinline__ double reduce_fast(double x, int &n)
-{
-    const double r = x * 0x1.45f306dc9c883p+23;
-    n = (__double2int_rz(r) + 0x800000) >> 24;
-    return fma(-(double)n, 0x1.921fb54442d18p+0, x);
-}
-
-// quadrant -> (is cosine, table); shared by sinf (flip = 0) and cosf (flip = 1)
-__device__ __forceinline__ float sincos_one(float y, int flip)
-{
-    double x = (double)y;
-    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) // |y| < pi / 4
-    {
-        if (abstop12(y) < abstop12(0x1p-12f))
-        {
-            return flip ? 1.0f : y;
-        }
-        return sinf_poly(x, x * x, kSinCos0, flip);
-    }
-    if (abstop12(y) < abstop12(120.0f))
-    {
-        int n;
-        x = reduce_fast(x, n);
-        const double s = (n & 3) == 1 || (n & 3) == 2 ? -1.0 : 1.0; // sign[n & 3] = {1, -1, -1, 1}
-        const double *p = (n & 2) ? kSinCos1 : kSinCos0;
-        return sinf_poly(x * s, x * x, p, n ^ flip);
-    }
-    // huge arguments (reduce_large) never reach the path tracer: correctly rounded instead
-    return (float)(flip ? cos(x) : sin(x));
+    const double c = fma(x4, 0x1.55553e1068f19p-5, c1); // c1 + x4 c2
+    float C = (float)fma(x6, c2, c);
+    C = (n & 2) ? -C : C;
+    const bool tiny = abstop12(y) < abstop12(0x1p-12f);
+    sin_out = tiny ? y : ((n & 1) ? C : S);
+    cos_out = tiny ? 1.0f : ((n & 1) ? S : C);
 }
 } // namespace glibc
 
-static __device__ __noinline__ float glibc_sinf(float y) { return glibc::sincos_one(y, 0); }
-static __device__ __noinline__ float glibc_cosf(float y) { return glibc::sincos_one(y, 1); }
+// |y| >= 120 (glibc: reduce_large) never reaches the path tracer: correctly rounded instead. A function of its own: CUDA's
+// double sin / cos carry a Payne-Hanek path whose registers the fast routine would otherwise be charged with.
+static __device__ __noinline__ void glibc_sincosf_huge(float y, float *s, float *c)
+{
+    *s = (float)sin((double)y);
+    *c = (float)cos((double)y);
+}
 static __device__ __noinline__ void glibc_sincosf(float y, float *s, float *c)
 {
-    *s = glibc::sincos_one(y, 0);
-    *c = glibc::sincos_one(y, 1);
+    if (glibc::abstop12(y) < glibc::abstop12(120.0f))
+    {
+        glibc::sincos_fast(y, *s, *c);
+        return;
+    }
+    glibc_sincosf_huge(y, s, c);
 }
 
-// __powf (e_powf.c) for y > 0 finite and x >= 0: log2_inline, y * log2(x), exp2_inline
+// __powf (e_powf.c) for finite y > 0 that is not an integer (2.4, 0.45, 1 / 2.4: the sRGB curves): log2_inline,
+// y * log2(x), exp2_inline, with the routine's own handling of zero, subnormal, infinite and NaN x and of overflow and
+// underflow; a negative x is a domain error for such y (NaN). No call into CUDA's double pow(): its registers would be
+// charged to every caller.
 static __device__ __noinline__ float glibc_powf(float x, float y)
 {
     using namespace glibc;
@@ -96,9 +95,9 @@ static __device__ __noinline__ float glibc_powf(float x, float y)
         {
             return 0.f; // x^y for +0 and y > 0
         }
-        if (ix >= 0x00800000u)
+        if (ix >= 0x7f800000u)
         {
-            return (float)pow((double)x, (double)y); // negative, infinite, NaN: not on the path tracer's paths
+            return ix == 0x7f800000u ? x : (ix == 0x80000000u ? 0.f : __int_as_float(0x7fc00000)); // +inf; -0; x < 0 or NaN
         }
         ix = __float_as_uint(x * 0x1p23f) & 0x7fffffffu; // normalise a subnormal: the exponent becomes negative
         ix -= 23u << 23;
@@ -109,7 +108,7 @@ static __device__ __noinline__ float glibc_powf(float x, float y)
     const unsigned top = tmp & 0xff800000u;
     const unsigned iz = ix - top;
     const int k = (int)top >> 23; // arithmetic shift
-    const double invc = __ldg(kPowLog2Tab + 2 * i), logc = __ldg(kPowLog2Tab + 2 * i + 1);
+    const double invc = SPK_GLIBC_LD(kPowLog2Tab + 2 * i), logc = SPK_GLIBC_LD(kPowLog2Tab + 2 * i + 1);
     const double z = (double)__uint_as_float(iz);
     const double r = fma(z, invc, -1.0);
     const double y0 = logc + (double)k;
@@ -124,14 +123,22 @@ static __device__ __noinline__ float glibc_powf(float x, float y)
     if (((unsigned long long)__double_as_longlong(ylogx) >> 47 & 0xffffull) >=
         ((unsigned long long)__double_as_longlong(126.0) >> 47)) // |y log2 x| >= 126: overflow / underflow handling
     {
-        return (float)pow((double)x, (double)y);
+        if (ylogx > 0x1.fffffffd1d571p+6)
+        {
+            return __int_as_float(0x7f800000); // overflow
+        }
+        if (ylogx <= -150.0)
+        {
+            return 0.f; // underflow
+        }
+        // between: a subnormal result, rounded by the conversion at the end like glibc's
     }
     // exp2_inline
     double kd = ylogx + kExp2ShiftScaled;
     const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
     kd -= kExp2ShiftScaled;
     const double rr = ylogx - kd;
-    unsigned long long tb = __ldg(kExp2Tab + (ki % 32ull));
+    unsigned long long tb = SPK_GLIBC_LD(kExp2Tab + (ki % 32ull));
     tb += ki << (52 - 5);
     const double s = __longlong_as_double((long long)tb);
     const double zz = fma(0x1.c6af84b912394p-5, rr, 0x1.ebfce50fac4f3p-3); // C[0] r + C[1]

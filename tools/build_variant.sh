@@ -9,7 +9,7 @@ NVFLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=
 objs=""
 for f in spk_api spk_trace spk_render spk_wavefront spk_denoise spk_group spk_build; do
   case $f in
-    spk_trace|spk_wavefront) /usr/local/cuda/bin/nvcc $NVFLAGS "$@" -c csrc/$f.cu -o build_$tag/$f.o 2> build_$tag/$f.ptxas.log || { cat build_$tag/$f.ptxas.log; exit 1; }
+    spk_trace|spk_wavefront|spk_render) /usr/local/cuda/bin/nvcc $NVFLAGS "$@" -c csrc/$f.cu -o build_$tag/$f.o 2> build_$tag/$f.ptxas.log || { cat build_$tag/$f.ptxas.log; exit 1; }
        objs="$objs build_$tag/$f.o";;
     *) objs="$objs build/$f.o";;
   esac
