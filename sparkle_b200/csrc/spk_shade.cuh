@@ -42,8 +42,13 @@ static __device__ __forceinline__ float ref_pow(float x, float y)
 // ~0.1 % of the arguments, by one ulp, in a factor no branch depends on; the full routine would cost 10x as much here)
 __device__ __forceinline__ float ref_pow5(float x)
 {
+#ifdef SPK_POW5_GLIBC
+    const float r = glibc_powf(fabsf(x), 5.f); // odd integer exponent: the sign of x carries over (e_powf.c sign_bias)
+    return signbit(x) ? -r : r;
+#else
     double d = (double)x, d2 = d * d;
     return (float)(d2 * d2 * d);
+#endif
 }
 
 // ---- XoshiroCpp::Xoshiro128Plus seeded through SplitMix64, sampler::RandomUnit ----

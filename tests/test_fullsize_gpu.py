@@ -83,6 +83,10 @@ def test_c2_full_resolution(oracle, monkeypatch):
     psnr = 10 * np.log10(max(ref[..., :3].max(), 1e-6) ** 2 / max(mse, 1e-30))
     print(f"C2 1920x1080 {spp} spp: mean rel err {rel.mean():.2e}, PSNR {psnr:.1f} dB, pixels > 1e-4: {(rel > 1e-4).mean():.2e}")
     assert rel.mean() <= 1e-3 and psnr > 40
+    # the device computes sin / cos / pow the way glibc does (csrc/spk_glibc_math.cuh): against the reference build on the
+    # same libm the frame is the same image, not merely a close one (what is left is Schlick's pow(x, 5): one ulp, rarely)
+    if oracle.kind == "reference":
+        assert rel.mean() <= 1e-7 and (rel > 1e-6).mean() < 1e-4 and psnr > 120, (rel.mean(), psnr)
     import parity_report as PR
     PR.report(f"c2_1920x1080_{spp}spp_vs_{oracle.kind}", whole, ref)
     ctx.close()

@@ -70,6 +70,10 @@ def test_c5_room_depth32_gate(oracle, port_device_libm):
     assert m_ref["mean_rel"] <= 1.25 * m_libm["mean_rel"] + 1e-4, (m_ref, "libm share", m_libm)
     assert m_ref["mean_rel_lit"] <= MEAN_REL_TOL and m_ref["rel_l1"] <= MEAN_REL_TOL, m_ref
     assert m_ref["frac_gt_1e4"] < 0.005 and m_ref["psnr"] > 60.0, m_ref
+    # (3) since the device restates glibc's sinf / cosf / powf (csrc/spk_glibc_math.cuh) there is no libm share left to
+    # separate out: against the reference build the depth-32 room is the same image (Schlick's pow(x, 5) aside)
+    if oracle.kind == "reference":
+        assert m_ref["mean_rel"] <= 1e-7 and m_ref["frac_identical"] > 0.999, m_ref
 
 
 @pytest.mark.parametrize("name", ["testscene", "city"])
