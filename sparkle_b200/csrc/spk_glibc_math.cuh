@@ -71,7 +71,11 @@ static __device__ __noinline__ void glibc_sincosf_huge(float y, float *s, float 
     *s = (float)sin((double)y);
     *c = (float)cos((double)y);
 }
+#ifdef SPK_INLINE_SINCOS
+static __device__ __forceinline__ void glibc_sincosf(float y, float *s, float *c)
+#else
 static __device__ __noinline__ void glibc_sincosf(float y, float *s, float *c)
+#endif
 {
     if (glibc::abstop12(y) < glibc::abstop12(120.0f))
     {
@@ -85,7 +89,11 @@ static __device__ __noinline__ void glibc_sincosf(float y, float *s, float *c)
 // y * log2(x), exp2_inline, with the routine's own handling of zero, subnormal, infinite and NaN x and of overflow and
 // underflow; a negative x is a domain error for such y (NaN). No call into CUDA's double pow(): its registers would be
 // charged to every caller.
+#ifdef SPK_INLINE_POW
+static __device__ __forceinline__ float glibc_powf(float x, float y)
+#else
 static __device__ __noinline__ float glibc_powf(float x, float y)
+#endif
 {
     using namespace glibc;
     unsigned ix = __float_as_uint(x);
