@@ -105,7 +105,8 @@ static __device__ __noinline__ float glibc_powf(float x, float y)
         }
         if (ix >= 0x7f800000u)
         {
-            return ix == 0x7f800000u ? x : (ix == 0x80000000u ? 0.f : __int_as_float(0x7fc00000)); // +inf; -0; x < 0 or NaN
+            // +-inf -> x * x = +inf; -0 -> +0 (y is not an odd integer); finite x < 0: domain error; NaN stays NaN
+            return (ix & 0x7fffffffu) == 0x7f800000u ? __int_as_float(0x7f800000) : (ix == 0x80000000u ? 0.f : __int_as_float(0x7fc00000));
         }
         ix = __float_as_uint(x * 0x1p23f) & 0x7fffffffu; // normalise a subnormal: the exponent becomes negative
         ix -= 23u << 23;

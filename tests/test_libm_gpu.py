@@ -50,4 +50,19 @@ def test_device_sin_cos_pow_equal_glibc():
         want = np.array([m.powf(float(a), float(np.float32(yv))) for a in xs], np.float32)
         bad = np.nonzero(got.view(np.uint32) != want.view(np.uint32))[0]
         assert bad.size == 0, (yv, bad.size, xs[bad[:5]], got[bad[:5]], want[bad[:5]])
+    # the special cases of e_powf.c for a positive non-integer exponent: zeros, subnormals, overflow, underflow (down to a
+    # subnormal result), infinity, NaN, negative bases (domain error)
+    edge = np.array([0.0, -0.0, 1e-45, 1e-40, 1.1754944e-38, 1e-30, 1e-20, 1e-16, 1e16, 1e20, 1e30, 3.4e38, np.inf, np.nan,
+                     -1.0, -0.5, -np.inf, 1.0, 0.99999994, 1.0000001], np.float32)
+    for yv in (2.4, 0.45):
+        got = device(ctx, 2, edge, np.full(edge.shape, yv, np.float32))
+        want = np.array([m.powf(float(a), float(np.float32(yv))) for a in edge], np.float32)
+        same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
+        assert same.all(), (yv, edge[~same], got[~same], want[~same])
+    # sin / cos beyond the fast range fall back to a correctly rounded value: within one ulp of glibc's
+    big = np.array([120.0, 1000.0, -5000.5, 1e6], np.float32)
+    for op, f in ((0, m.sinf), (1, m.cosf)):
+        got = device(ctx, op, big)
+        want = np.array([f(float(a)) for a in big], np.float32)
+        assert np.all(np.abs(got.view(np.int32) - want.view(np.int32)) <= 1), (got, want)
     ctx.close()
