@@ -77,8 +77,8 @@ int orc_kat_decode_hdr(const unsigned char *data, uint32_t size, uint32_t *width
                        uint64_t capacity_halves);
 int orc_kat_cook_sky_cube(const uint16_t *equirect_rgba_half, uint32_t width, uint32_t height, uint32_t size,
                           uint16_t *faces_out);
-/* "port" only: 0 = glibc float sin/cos/pow as the reference calls them (default), 1 = evaluated in double and rounded
- * once, as the CUDA path does (separates operation-order parity from one-ulp libm drift; oracle.cpp g_libm_mode) */
+/* "port" only: 0 = glibc float sin/cos/pow as the reference calls them (default), 1 = what the CUDA path computes: the same
+ * (csrc/spk_glibc_math.cuh), except Schlick's pow(x, 5.f) as an exact product rounded once (oracle.cpp g_libm_mode) */
 int orc_set_libm(uint32_t mode);
 
 /* a6-a9: closest hit of a ray batch. threads<=1 runs on the calling thread. */

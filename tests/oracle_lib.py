@@ -101,8 +101,8 @@ class Oracle:
         return out
 
     def set_libm(self, device_libm):
-        """port only: False = glibc float sin/cos/pow like the reference (default); True = double, rounded once, like
-        the CUDA path. Process-wide: reset it in a finally block."""
+        """port only: False = glibc float sin/cos/pow like the reference (default); True = what the CUDA path computes (the
+        same, except Schlick's pow(x, 5.f) as an exact product rounded once). Process-wide: reset it in a finally block."""
         assert self.kind == "port"
         self.lib.orc_set_libm(1 if device_libm else 0)
 

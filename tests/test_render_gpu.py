@@ -1,7 +1,7 @@
 """GPU parity of the path tracer: spk_cuda_render / spk_cuda_resolve vs the oracle's CPURenderer on the same scene,
 camera and sample seeds. Tolerance (BASELINE.json north_star): mean relative per-pixel error <= 1e-3 at equal spp with
-identical sample streams; PSNR reported. Most pixels are expected to agree to float rounding (the device evaluates sin,
-cos and pow in double and rounds once; glibc's float versions differ by one ulp for ~1 % of arguments)."""
+identical sample streams; PSNR reported. Against the reference build the images are expected to be the same (the device
+computes sin, cos and pow the way glibc does, csrc/spk_glibc_math.cuh): asserted to 1e-7 / 99.9 % identical pixels."""
 import numpy as np
 import pytest
 
