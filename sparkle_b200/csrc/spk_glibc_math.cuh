@@ -66,23 +66,25 @@ __device__ __forceinline__ void sincos_fast(float y, float &sin_out, float &cos_
 
 // |y| >= 120 (glibc: reduce_large) never reaches the path tracer: correctly rounded instead. A function of its own: CUDA's
 // double sin / cos carry a Payne-Hanek path whose registers the fast routine would otherwise be charged with.
-static __device__ __noinline__ void glibc_sincosf_huge(float y, float *s, float *c)
+static __device__ __noinline__ float2 glibc_sincosf_huge(float y)
 {
-    *s = (float)sin((double)y);
-    *c = (float)cos((double)y);
+    return make_float2((float)sin((double)y), (float)cos((double)y));
 }
+// {sin y, cos y}, returned in registers: with pointer arguments the caller's two floats lived in local memory (a store and a
+// load through L1 per call, since the function is not inlined)
 #ifdef SPK_INLINE_SINCOS
-static __device__ __forceinline__ void glibc_sincosf(float y, float *s, float *c)
+static __device__ __forceinline__ float2 glibc_sincosf(float y)
 #else
-static __device__ __noinline__ void glibc_sincosf(float y, float *s, float *c)
+static __device__ __noinline__ float2 glibc_sincosf(float y)
 #endif
 {
     if (glibc::abstop12(y) < glibc::abstop12(120.0f))
     {
-        glibc::sincos_fast(y, *s, *c);
-        return;
+        float2 r;
+        glibc::sincos_fast(y, r.x, r.y);
+        return r;
     }
-    glibc_sincosf_huge(y, s, c);
+    return glibc_sincosf_huge(y);
 }
 
 // __powf (e_powf.c) for finite y > 0 that is not an integer (2.4, 0.45, 1 / 2.4: the sRGB curves): log2_inline,

@@ -32,7 +32,9 @@ constexpr float kInvSqrt3 = 0.577350258827209473f; // std::numbers::inv_sqrt3_v<
 // pow call sites would otherwise be inlined into every kernel).
 static __device__ __forceinline__ void ref_sincos(float x, float *s, float *c)
 {
-    glibc_sincosf(x, s, c);
+    const float2 sc = glibc_sincosf(x);
+    *s = sc.x;
+    *c = sc.y;
 }
 static __device__ __forceinline__ float ref_pow(float x, float y)
 {
