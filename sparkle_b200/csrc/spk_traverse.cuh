@@ -148,9 +148,11 @@ constexpr int kThreadStack = 76;                  // 32 TLAS + 1 leaf remainder 
 // object-space one and parks the world one under a marker, popping the marker restores it. The visit order is the
 // reference's (bvh::v2: near child first, far child pushed; TLAS leaf -> primitives in order -> each BLAS to
 // exhaustion). Measured against the nested form on B200: C2 -5 %, room -14 %, city-10M megakernel -19 %.
-template <bool CULL, bool COUNT>
+// SLAB: the world-space slab constants live in `world_slab` (six words, `slab_stride` apart: a column of shared memory), written
+// once per ray; otherwise they are parked on the stack at every instance entry (7 local stores in, 6 local loads out).
+template <bool CULL, bool COUNT, bool SLAB = false>
 __device__ __forceinline__ void trace_closest(const DScene &sc, V3 wo, V3 wd, Hit &best, uint32_t *stack,
-                                              TraceCounters &cnt)
+                                              TraceCounters &cnt, float *world_slab = nullptr, int slab_stride = 1)
 {
     best.t = SPK_FLT_MAX;
     best.u = 0.f;
@@ -169,6 +171,15 @@ __device__ __forceinline__ void trace_closest(const DScene &sc, V3 wo, V3 wd, Hi
     const float4 *__restrict__ pairs = sc.pairs;
     const float4 *__restrict__ tris = sc.tris;
     SlabRay sr = make_slab_ray(wo, wd);
+    if (SLAB)
+    {
+        world_slab[0] = sr.ix;
+        world_slab[slab_stride] = sr.iy;
+        world_slab[2 * slab_stride] = sr.iz;
+        world_slab[3 * slab_stride] = sr.ox;
+        world_slab[4 * slab_stride] = sr.oy;
+        world_slab[5 * slab_stride] = sr.oz;
+    }
     V3 lo = wo, ld = wd;             // the ray in the space of the tree being traversed
     uint32_t inst = SPK_INVALID_ID;  // the instance whose BLAS is being traversed; none: TLAS level
     // Both markers have a non-zero low nibble, so the inner loop leaves on them as it does on a leaf and a pop is a
@@ -228,13 +239,25 @@ __device__ __forceinline__ void trace_closest(const DScene &sc, V3 wo, V3 wd, Hi
             }
             // kLeaveInstance: back at the TLAS level, the world slab constants were parked under the marker
             inst = SPK_INVALID_ID;
-            sp -= 6;
-            sr.ix = __uint_as_float(stack[sp]);
-            sr.iy = __uint_as_float(stack[sp + 1]);
-            sr.iz = __uint_as_float(stack[sp + 2]);
-            sr.ox = __uint_as_float(stack[sp + 3]);
-            sr.oy = __uint_as_float(stack[sp + 4]);
-            sr.oz = __uint_as_float(stack[sp + 5]);
+            if (SLAB)
+            {
+                sr.ix = world_slab[0];
+                sr.iy = world_slab[slab_stride];
+                sr.iz = world_slab[2 * slab_stride];
+                sr.ox = world_slab[3 * slab_stride];
+                sr.oy = world_slab[4 * slab_stride];
+                sr.oz = world_slab[5 * slab_stride];
+            }
+            else
+            {
+                sp -= 6;
+                sr.ix = __uint_as_float(stack[sp]);
+                sr.iy = __uint_as_float(stack[sp + 1]);
+                sr.iz = __uint_as_float(stack[sp + 2]);
+                sr.ox = __uint_as_float(stack[sp + 3]);
+                sr.oy = __uint_as_float(stack[sp + 4]);
+                sr.oz = __uint_as_float(stack[sp + 5]);
+            }
             sr.nx = signbit(wd.x);
             sr.ny = signbit(wd.y);
             sr.nz = signbit(wd.z);
@@ -287,14 +310,21 @@ __device__ __forceinline__ void trace_closest(const DScene &sc, V3 wo, V3 wd, Hi
                     inv[4 * k + 2] = r.z;
                     inv[4 * k + 3] = r.w;
                 }
-                stack[sp] = __float_as_uint(sr.ix);
-                stack[sp + 1] = __float_as_uint(sr.iy);
-                stack[sp + 2] = __float_as_uint(sr.iz);
-                stack[sp + 3] = __float_as_uint(sr.ox);
-                stack[sp + 4] = __float_as_uint(sr.oy);
-                stack[sp + 5] = __float_as_uint(sr.oz);
-                stack[sp + 6] = kLeaveInstance;
-                sp += 7;
+                if (SLAB)
+                {
+                    stack[sp++] = kLeaveInstance;
+                }
+                else
+                {
+                    stack[sp] = __float_as_uint(sr.ix);
+                    stack[sp + 1] = __float_as_uint(sr.iy);
+                    stack[sp + 2] = __float_as_uint(sr.iz);
+                    stack[sp + 3] = __float_as_uint(sr.ox);
+                    stack[sp + 4] = __float_as_uint(sr.oy);
+                    stack[sp + 5] = __float_as_uint(sr.oz);
+                    stack[sp + 6] = kLeaveInstance;
+                    sp += 7;
+                }
                 lo = xform_point(inv, wo);
                 ld = xform_dir(inv, wd);
                 sr = make_slab_ray(lo, ld);
