@@ -91,13 +91,10 @@ static __device__ __noinline__ float2 glibc_sincosf(float y)
 // y * log2(x), exp2_inline, with the routine's own handling of zero, subnormal, infinite and NaN x and of overflow and
 // underflow; a negative x is a domain error for such y (NaN). No call into CUDA's double pow(): its registers would be
 // charged to every caller.
-#ifdef SPK_INLINE_POW
-static __device__ __forceinline__ float glibc_powf(float x, float y)
-#else
-static __device__ __noinline__ float glibc_powf(float x, float y)
-#endif
+namespace glibc
 {
-    using namespace glibc;
+__device__ __forceinline__ float powf_core(float x, float y)
+{
     unsigned ix = __float_as_uint(x);
     if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) // zero, subnormal, negative, infinite, NaN
     {
@@ -157,5 +154,11 @@ static __device__ __noinline__ float glibc_powf(float x, float y)
     double out = fma(0x1.62e42ff0c52d6p-1, rr, 1.0); // C[2] r + 1
     out = fma(zz, rr2, out);
     return (float)(out * s);
+}
+} // namespace glibc
+
+static __device__ __noinline__ float glibc_powf(float x, float y)
+{
+    return glibc::powf_core(x, y);
 }
 } // namespace spk
