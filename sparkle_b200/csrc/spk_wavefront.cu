@@ -564,7 +564,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
     // ray sorting: three queue buffers rotate. The queue an iteration fills is sorted by ray key into the spare buffer,
     // which wf_extend and the next wf_shade read; the counts in the control block stay indexed by parity.
     uint32_t *q_cur = st.queue[0], *q_nxt = st.queue[1], *q_spare = sort.queue_spare;
-    uint32_t sort_items = slots; // upper bound of a queue's length: all slots until the work runs out, then what is left
+    uint32_t queue_bound = slots; // upper bound of a queue's length: all slots until the work runs out, then what is left
     WfCtrl h{};
     for (;; chunk = chunk_next)
     {
@@ -574,7 +574,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
             st.queue[cur ^ 1u] = q_nxt;
             // the grid covers what the queue can hold: all slots while new paths start, then (the queue only shrinks) its
             // length at the host's last look
-            wf_shade_kernel<<<(sort_items + kShadeThreads - 1) / kShadeThreads, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur,
+            wf_shade_kernel<<<(queue_bound + kShadeThreads - 1) / kShadeThreads, kShadeThreads, 0, s>>>(ctx->scene, a, st, cur,
                                                                                                          ctx->d_accum);
             wf_regen_kernel<<<regen_blocks, kShadeThreads, 0, s>>>(ctx->camera, a, st, cur ^ 1u);
             wf_advance_kernel<<<1, 1, 0, s>>>(st, cur, ctx->d_counters);
@@ -583,7 +583,7 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
             {
                 size_t bytes = sort.tmp_bytes;
                 SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sort.tmp, bytes, (const uint32_t *)st.keys, sort.keys_sorted,
-                                                             (const uint32_t *)q_nxt, q_spare, sort_items, 0, sort.end_bit, s));
+                                                             (const uint32_t *)q_nxt, q_spare, queue_bound, 0, sort.end_bit, s));
                 uint32_t *t = q_nxt;
                 q_nxt = q_spare;
                 q_spare = t;
@@ -603,9 +603,9 @@ static int wf_run(SpkContext *ctx, const WfArgs &a, WfState st, const WfSort &so
         {
             break;
         }
-        if (h.work_next >= h.work_total && h.n_queue[cur] < sort_items)
+        if (h.work_next >= h.work_total && h.n_queue[cur] < queue_bound)
         {
-            sort_items = h.n_queue[cur]; // no new paths: the queue only shrinks from here
+            queue_bound = h.n_queue[cur]; // no new paths: the queue only shrinks from here
         }
     }
     return SPK_OK;
