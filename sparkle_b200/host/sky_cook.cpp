@@ -182,6 +182,12 @@ bool DecodeRadianceHdr(const uint8_t *data, size_t size, uint32_t &width_out, ui
         error = "too large";
         return false;
     }
+    // stbi__mad4sizes_valid(width, height, 4, sizeof(float)): the decoded image must fit an int
+    if (uint64_t(width) * uint64_t(height) * 4u * sizeof(float) > uint64_t(0x7fffffff))
+    {
+        error = "too large";
+        return false;
+    }
     pixels.assign(size_t(width) * size_t(height) * 4, 0);
     width_out = uint32_t(width);
     height_out = uint32_t(height);

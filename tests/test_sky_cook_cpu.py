@@ -67,7 +67,8 @@ def test_decode_equals_reference():
     good = H.write_hdr(H.float_to_rgbe(H.make_sky(64, 16)))
     for name, data in [("no identifier", b"#?RADIANT\n" + good[11:]), ("no format line", good.replace(b"FORMAT=32-bit_rle_rgbe\n", b"")),
                        ("other layout", good.replace(b"-Y 16 +X 64", b"+Y 16 +X 64")),
-                       ("wrong scanline length", good.replace(bytes([2, 2, 0, 64]), bytes([2, 2, 0, 63]), 1))]:
+                       ("wrong scanline length", good.replace(bytes([2, 2, 0, 64]), bytes([2, 2, 0, 63]), 1)),
+                       ("decoded size beyond an int", good.replace(b"-Y 16 +X 64", b"-Y 16000 +X 16000"))]:
         assert ref.kat_decode_hdr(data) is None, name
         assert host_decode(data) is None, name
     # (a flat file of width >= 8, the "flat" case above, is read through stb_image's mid-file fallback: its first scanline
