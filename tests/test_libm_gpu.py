@@ -13,6 +13,12 @@ from sparkle_b200.device import CudaContext
 pytestmark = pytest.mark.gpu
 
 
+# The device restates the FMA build of glibc's routines, which the dynamic loader picks on every CPU with FMA (all hosts of
+# this pool: 0 differences). On a CPU without FMA libm runs the same source uncontracted and ~5 arguments in 10^7 differ by
+# one ulp (tools/glibc_math_probe.cpp -DFMA=0): tolerated, so that such a host does not turn the suite red.
+FEW = 3 if "fma" not in open("/proc/cpuinfo").read() else 0
+
+
 def host_libm():
     m = C.CDLL(ctypes.util.find_library("m") or "libm.so.6")
     for f in (m.sinf, m.cosf):
@@ -41,7 +47,8 @@ def test_device_sin_cos_pow_equal_glibc():
         got = device(ctx, op, angles)
         want = np.array([f(float(a)) for a in angles], np.float32)
         bad = np.nonzero(got.view(np.uint32) != want.view(np.uint32))[0]
-        assert bad.size == 0, (name, bad.size, angles[bad[:5]], got[bad[:5]], want[bad[:5]])
+        assert bad.size <= FEW and np.all(np.abs(got.view(np.int32)[bad] - want.view(np.int32)[bad]) <= 1), \
+            (name, bad.size, angles[bad[:5]], got[bad[:5]], want[bad[:5]])
     # sRGB decode ((c + 0.055) / 1.055)^2.4 on (0, 1], encode r^0.45 on [0, 1] incl. 0 and subnormals, and other exponents
     xs = np.concatenate([g.uniform(0.04, 1.0, n), g.uniform(0, 1.0, n), [0.0, 1.0, 1e-39, 1e-45, 0.5, 2.0, 100.0]]).astype(np.float32)
     for yv in (2.4, 0.45, 1.0 / 2.4, 5.0):
@@ -49,7 +56,8 @@ def test_device_sin_cos_pow_equal_glibc():
         got = device(ctx, 2, xs, ys)
         want = np.array([m.powf(float(a), float(np.float32(yv))) for a in xs], np.float32)
         bad = np.nonzero(got.view(np.uint32) != want.view(np.uint32))[0]
-        assert bad.size == 0, (yv, bad.size, xs[bad[:5]], got[bad[:5]], want[bad[:5]])
+        assert bad.size <= FEW and np.all(np.abs(got.view(np.int32)[bad] - want.view(np.int32)[bad]) <= 1), \
+            (yv, bad.size, xs[bad[:5]], got[bad[:5]], want[bad[:5]])
     # the special cases of e_powf.c for a positive non-integer exponent: zeros, subnormals, overflow, underflow (down to a
     # subnormal result), infinity, NaN, negative bases (domain error)
     edge = np.array([0.0, -0.0, 1e-45, 1e-40, 1.1754944e-38, 1e-30, 1e-20, 1e-16, 1e16, 1e20, 1e30, 3.4e38, np.inf, np.nan,
