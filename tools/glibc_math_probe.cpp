@@ -16,60 +16,35 @@ static inline uint32_t asuint(float f) { uint32_t u; memcpy(&u, &f, 4); return u
 static inline float asfloat(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 static inline uint64_t asuint64(double f) { uint64_t u; memcpy(&u, &f, 8); return u; }
 static inline double asdouble(uint64_t u) { double f; memcpy(&f, &u, 8); return f; }
-// table layout in the binary: sign[4], hpi_inv, hpi, c0, c1, s1, c2, s2, c3, s3, c4
-struct SC { const double *t; double c0() const {return t[6];} double c1() const {return t[7];} double s1() const {return t[8];}
-  double c2() const {return t[9];} double s2() const {return t[10];} double c3() const {return t[11];} double s3() const {return t[12];} double c4() const {return t[13];} };
-static inline float sinf_poly(double x, double x2, SC p, int n)
-{
-    if ((n & 1) == 0) {
-        double x3 = x * x2;
-        double s1 = mad(x2, p.s3(), p.s2());
-        double x7 = x3 * x2;
-        double s = mad(x3, p.s1(), x);
-        return (float)mad(x7, s1, s);
-    } else {
-        double x4 = x2 * x2;
-        double c2 = mad(x2, p.c4(), p.c3());
-        double c1 = mad(x2, p.c1(), p.c0());
-        double x6 = x4 * x2;
-        double c = mad(x4, p.c2(), c1);
-        return (float)mad(x6, c2, c);
-    }
-}
 static inline uint32_t abstop12(float x) { return (asuint(x) >> 20) & 0x7ff; }
-static inline double reduce_fast(double x, const double *t, int *np)
+// the device's sincos_fast (spk_glibc_math.cuh), statement for statement: branch-free, immediate coefficients, the cosine
+// polynomial of __sincosf_table[1] as the negated one of table [0]
+static inline void sincos_fast(float y, float &sin_out, float &cos_out)
 {
-    double r = x * t[4];
-    int n = ((int32_t)r + 0x800000) >> 24;
-    *np = n;
-    return FMA ? std::fma(-(double)n, t[5], x) : x - n * t[5];
+    const double x0 = (double)y;
+    const double r = x0 * 0x1.45f306dc9c883p+23;
+    const int n = ((int32_t)r + 0x800000) >> 24;
+    const double x = mad(-(double)n, 0x1.921fb54442d18p+0, x0);
+    const double xs = ((n + 1) & 2) ? -x : x;
+    const double x2 = x * x;
+    const double x3 = xs * x2;
+    const double s1 = mad(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
+    const double x5 = x3 * x2;
+    const double s = mad(x3, -0x1.555545995a603p-3, xs);
+    const float S = (float)mad(x5, s1, s);
+    const double x4 = x2 * x2;
+    const double c2 = mad(x2, 0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10);
+    const double c1 = mad(x2, -0x1.ffffffd0c621cp-2, 1.0);
+    const double x6 = x4 * x2;
+    const double c = mad(x4, 0x1.55553e1068f19p-5, c1);
+    float C = (float)mad(x6, c2, c);
+    C = (n & 2) ? -C : C;
+    const bool tiny = abstop12(y) < abstop12(0x1p-12f);
+    sin_out = tiny ? y : ((n & 1) ? C : S);
+    cos_out = tiny ? 1.0f : ((n & 1) ? S : C);
 }
-float my_sinf(float y)
-{
-    double x = y; int n;
-    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {
-        double s = x * x;
-        if (abstop12(y) < abstop12(0x1p-12f)) return y;
-        return sinf_poly(x, s, SC{kSinCos0}, 0);
-    }
-    x = reduce_fast(x, kSinCos0, &n);
-    double s = kSinCos0[n & 3];
-    SC p{(n & 2) ? kSinCos1 : kSinCos0};
-    return sinf_poly(x * s, x * x, p, n);
-}
-float my_cosf(float y)
-{
-    double x = y; int n;
-    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {
-        double x2 = x * x;
-        if (abstop12(y) < abstop12(0x1p-12f)) return 1.0f;
-        return sinf_poly(x, x2, SC{kSinCos0}, 1);
-    }
-    x = reduce_fast(x, kSinCos0, &n);
-    double s = kSinCos0[n & 3];
-    SC p{(n & 2) ? kSinCos1 : kSinCos0};
-    return sinf_poly(x * s, x * x, p, n ^ 1);
-}
+float my_sinf(float y) { float s, c; sincos_fast(y, s, c); return s; }
+float my_cosf(float y) { float s, c; sincos_fast(y, s, c); return c; }
 float my_powf(float x, float y)
 {
     uint32_t ix = asuint(x);
@@ -106,11 +81,18 @@ float my_powf(float x, float y)
     out = out * s;
     return (float)out;
 }
-int main()
+int main(int argc, char **argv)
 {
+    // the immediates above are __sincosf_table[0]; table [1] is it with the cosine coefficients negated
+    const double imm[8] = {1.0, -0x1.ffffffd0c621cp-2, -0x1.555545995a603p-3, 0x1.55553e1068f19p-5, 0x1.1107605230bc4p-7,
+                           -0x1.6c087e89a359dp-10, -0x1.994eb3774cf24p-13, 0x1.99343027bf8c3p-16};
+    for (int k = 0; k < 8; k++) {
+        const bool cosine = k == 0 || k == 1 || k == 3 || k == 5 || k == 7;
+        if (kSinCos0[6 + k] != imm[k] || kSinCos1[6 + k] != (cosine ? -imm[k] : imm[k])) { printf("table mismatch at %d\n", k); return 2; }
+    }
     uint64_t st = 88172645463325252ull;
     auto rnd = [&]() { st ^= st << 13; st ^= st >> 7; st ^= st << 17; return (double)(st >> 11) * (1.0 / 9007199254740992.0); };
-    long N = 50000000, bad_s = 0, bad_c = 0, bad_p1 = 0, bad_p2 = 0, bad_s2 = 0;
+    long N = argc > 1 ? atol(argv[1]) : 50000000, bad_s = 0, bad_c = 0, bad_p1 = 0, bad_p2 = 0, bad_s2 = 0;
     for (long k = 0; k < N; k++) {
         float th = (float)(rnd() * 6.283185307179586);
         if (my_sinf(th) != sinf(th)) bad_s++;
@@ -122,5 +104,5 @@ int main()
         if (my_powf(x, 0.45f) != powf(x, 0.45f)) bad_p2++;
     }
     printf("FMA=%d  N=%ld  sin(0..2pi) %ld  cos(0..2pi) %ld  sincos(+-100) %ld  pow(x,2.4) %ld  pow(x,0.45) %ld differ\n", FMA, N, bad_s, bad_c, bad_s2, bad_p1, bad_p2);
-    return 0;
+    return (bad_s + bad_c + bad_s2 + bad_p1 + bad_p2) ? 1 : 0;
 }
