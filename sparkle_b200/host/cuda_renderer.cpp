@@ -1155,13 +1155,17 @@ SpkHostApp *spk_host_app_create(const char *args, int device)
     {
         tokens.push_back(t);
     }
-    std::string scene_name = "testscene";
+    std::string scene_name = "testscene", sky_map;
     GltfOptions gltf_options;
     for (size_t k = 0; k + 1 < tokens.size(); k += 2)
     {
         if (tokens[k] == "--scene")
         {
             scene_name = tokens[k + 1];
+        }
+        else if (tokens[k] == "--sky_map")
+        {
+            sky_map = tokens[k + 1];
         }
         else if (tokens[k] == "--gltf_instancing")
         {
@@ -1213,6 +1217,12 @@ SpkHostApp *spk_host_app_create(const char *args, int device)
     {
         app->scene.SetSky(Vec3{0.5f, 0.7f, 1.0f});
         app->scene.GetCamera().SetupOrbit(Vec3{0, 0, 0}, 25.f, 10.f, -20.f);
+    }
+    // SceneManager::AddDefaultSky (SceneManager.cpp:229-243): the default sky of every scene that does not bring its own is
+    // a SkyLight with the map skymap/studio_garden.hdr. That asset is not in the mount: --sky_map names the .hdr to use.
+    if (!sky_map.empty() && !app->scene.SetSkyMapFile(sky_map))
+    {
+        return nullptr;
     }
     app->renderer = Renderer::CreateRenderer(app->config, &app->scene, device);
     if (!app->renderer)

@@ -200,5 +200,11 @@ def test_usd_scene_with_a_sky_map_through_the_host_app(tmp_path, oracle):
                     f"--scene {plain}")
     b.run()
     assert rel_err(b.read_linear(), ref) > 0.05
+    # --sky_map: the default sky of a scene without one (SceneManager::AddDefaultSky) from a user-supplied .hdr
+    c = app.HostApp(f"--pipeline cuda --width {w} --height {h} --max_spp {spp} --spp 2 --spatial_denoise false "
+                    f"--scene {plain} --sky_map {tmp_path / 'textures' / 'sky.hdr'}")
+    c.run()
+    assert c.scene.sky.has_map == 1 and np.array_equal(c.read_linear(), gpu)
     a.close()
     b.close()
+    c.close()
