@@ -480,28 +480,47 @@ struct WfSort // ray sorting: a third queue buffer, the sorted keys and cub's sc
 
 static int wf_reserve(SpkContext *ctx, uint32_t slots, WfState &st, WfSort &sort, uint32_t key_bits)
 {
-    // one allocation, carved into 256-byte aligned arrays
+    // one allocation, carved into 256-byte aligned arrays. The default pool is large (64 Mi slots = 7.2 GB): when the device
+    // cannot give that much the pool is halved until it fits (fewer slots only mean more, shorter iterations).
     auto al = [](size_t b) { return (b + 255) & ~size_t(255); };
-    const size_t b_rec = al(size_t(slots) * kRec * 16), b_u32 = al(size_t(slots) * 4);
-    size_t b_sort = 0;
+    size_t b_rec = 0, b_u32 = 0;
     sort.end_bit = int(3 * key_bits + 3);
-    if (key_bits)
+    for (;;)
     {
-        SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, sort.tmp_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
-                                                     (const uint32_t *)nullptr, (uint32_t *)nullptr, slots, 0, sort.end_bit,
-                                                     ctx->stream));
-        b_sort = 3 * b_u32 + al(sort.tmp_bytes);
-    }
-    const size_t total = b_rec + b_u32 * 3 + 256 + b_sort;
-    if (ctx->wf_slots != slots || ctx->wf_bytes < total)
-    {
+        b_rec = al(size_t(slots) * kRec * 16);
+        b_u32 = al(size_t(slots) * 4);
+        size_t b_sort = 0;
+        if (key_bits)
+        {
+            SPK_CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, sort.tmp_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+                                                         (const uint32_t *)nullptr, (uint32_t *)nullptr, slots, 0, sort.end_bit,
+                                                         ctx->stream));
+            b_sort = 3 * b_u32 + al(sort.tmp_bytes);
+        }
+        const size_t total = b_rec + b_u32 * 3 + 256 + b_sort;
+        if (ctx->wf_slots == slots && ctx->wf_bytes >= total)
+        {
+            break;
+        }
         cudaFree(ctx->wf_block);
         ctx->wf_block = nullptr;
         ctx->wf_slots = 0;
         ctx->wf_bytes = 0;
-        SPK_CUDA_TRY(cudaMalloc(&ctx->wf_block, total));
-        ctx->wf_slots = slots;
-        ctx->wf_bytes = total;
+        const cudaError_t e = cudaMalloc(&ctx->wf_block, total);
+        if (e == cudaSuccess)
+        {
+            ctx->wf_slots = slots;
+            ctx->wf_bytes = total;
+            break;
+        }
+        cudaGetLastError(); // clear the allocation failure
+        ctx->wf_block = nullptr;
+        if (e != cudaErrorMemoryAllocation || slots <= (1u << 20))
+        {
+            set_error(std::string("spk_cuda_render: wavefront slot pool: ") + cudaGetErrorString(e));
+            return e == cudaErrorMemoryAllocation ? SPK_ERR_OUT_OF_MEMORY : SPK_ERR_CUDA;
+        }
+        slots = ((slots / 2u) + 255u) & ~255u;
     }
     char *p = static_cast<char *>(ctx->wf_block);
     st.rec = reinterpret_cast<float4 *>(p);
